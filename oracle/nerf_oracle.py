@@ -1,0 +1,419 @@
+"""CPU oracle for the nerf_pl ray-rendering hot path.  TEST INFRASTRUCTURE ONLY.
+
+This file restates, in plain fp32 torch-on-CPU tensor arithmetic, the algorithm of
+the reference (ktiwary2/nerf_pl @ 99d40cb).  It is the *checker* for the CUDA path:
+only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import it.  Nothing under ``nerf_pl_b200/`` imports it
+and the product path has no CPU fallback.
+
+Parity pin: every function here is checked against outputs of the reference's own
+``models/*.py`` (imported from /root/reference by ``tests/make_golden.py`` in the
+build container, fixtures committed under ``tests/golden/``) by
+``tests/test_oracle_golden.py``.  Parity is therefore *pinned* (see DESIGN.md §3).
+
+Unlike the reference, every random tensor is an explicit argument, so that the
+oracle and the CUDA kernels can be driven with identical noise.  The order in which
+the reference draws them is (rendering.py:231, :178, :36, :41, :178):
+``u_perturb (N,Nc)`` -> ``noise_coarse (N,Nc)`` -> ``u_fine (N,Nf)`` ->
+``jitter_fine (N,Nf)`` -> ``noise_fine (N,Nc+Nf)``.
+
+All ``file:line`` citations are relative to /root/reference.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+Tensor = torch.Tensor
+
+
+# ---------------------------------------------------------------------------
+# models/nerf.py
+# ---------------------------------------------------------------------------
+
+def embed(x: Tensor, n_freqs: int, logscale: bool = True) -> Tensor:
+    """Positional encoding (models/nerf.py:21-38).
+
+    Output channel order: x, then for k in 0..L-1: sin(f_k x), cos(f_k x), with
+    f_k = 2**k (logscale, nerf.py:16-17) or linspace(1, 2**(L-1), L) (nerf.py:19).
+    """
+    if logscale:
+        freqs = 2.0 ** torch.linspace(0, n_freqs - 1, n_freqs)
+    else:
+        freqs = torch.linspace(1, 2 ** (n_freqs - 1), n_freqs)
+    pieces = [x]
+    for f in freqs:
+        fx = f * x
+        pieces.append(torch.sin(fx))
+        pieces.append(torch.cos(fx))
+    return torch.cat(pieces, dim=-1)
+
+
+def mlp_param_names(D: int = 8) -> List[str]:
+    """state_dict keys in the reference order (models/nerf.py:57-81)."""
+    names: List[str] = []
+    for i in range(D):
+        names += [f"xyz_encoding_{i + 1}.0.weight", f"xyz_encoding_{i + 1}.0.bias"]
+    names += ["xyz_encoding_final.weight", "xyz_encoding_final.bias",
+              "dir_encoding.0.weight", "dir_encoding.0.bias",
+              "sigma.weight", "sigma.bias", "rgb.0.weight", "rgb.0.bias"]
+    return names
+
+
+def init_mlp_params(D=8, W=256, in_xyz=63, in_dir=27, skips=(4,), generator=None) -> Dict[str, Tensor]:
+    """Random parameters in the reference checkpoint layout, nn.Linear default init
+    (uniform(-1/sqrt(fan_in), 1/sqrt(fan_in)) for weight and bias)."""
+    def lin(n_out, n_in):
+        bound = 1.0 / math.sqrt(n_in)
+        w = (torch.rand(n_out, n_in, generator=generator) * 2 - 1) * bound
+        b = (torch.rand(n_out, generator=generator) * 2 - 1) * bound
+        return w, b
+    p: Dict[str, Tensor] = {}
+    for i in range(D):
+        n_in = in_xyz if i == 0 else (W + in_xyz if i in skips else W)
+        p[f"xyz_encoding_{i + 1}.0.weight"], p[f"xyz_encoding_{i + 1}.0.bias"] = lin(W, n_in)
+    p["xyz_encoding_final.weight"], p["xyz_encoding_final.bias"] = lin(W, W)
+    p["dir_encoding.0.weight"], p["dir_encoding.0.bias"] = lin(W // 2, W + in_dir)
+    p["sigma.weight"], p["sigma.bias"] = lin(1, W)
+    p["rgb.0.weight"], p["rgb.0.bias"] = lin(3, W // 2)
+    return p
+
+
+def mlp_forward(p: Dict[str, Tensor], x: Tensor, sigma_only: bool = False,
+                D: int = 8, skips: Sequence[int] = (4,), in_xyz: int = 63) -> Tensor:
+    """NeRF.forward (models/nerf.py:83-124).  Skip concat puts the encoding FIRST
+    (nerf.py:108-109); sigma is raw (nerf.py:112); rgb is sigmoid (nerf.py:79-81)."""
+    F = torch.nn.functional
+    enc = x[..., :in_xyz]
+    h = enc
+    for i in range(D):
+        if i in skips:
+            h = torch.cat([enc, h], dim=-1)
+        h = torch.relu(F.linear(h, p[f"xyz_encoding_{i + 1}.0.weight"], p[f"xyz_encoding_{i + 1}.0.bias"]))
+    sigma = F.linear(h, p["sigma.weight"], p["sigma.bias"])
+    if sigma_only:
+        return sigma
+    feat = F.linear(h, p["xyz_encoding_final.weight"], p["xyz_encoding_final.bias"])
+    d = torch.relu(F.linear(torch.cat([feat, x[..., in_xyz:]], dim=-1),
+                            p["dir_encoding.0.weight"], p["dir_encoding.0.bias"]))
+    rgb = torch.sigmoid(F.linear(d, p["rgb.0.weight"], p["rgb.0.bias"]))
+    return torch.cat([rgb, sigma], dim=-1)
+
+
+# ---------------------------------------------------------------------------
+# models/rendering.py
+# ---------------------------------------------------------------------------
+
+def stratified_z(rays: Tensor, n_samples: int, use_disp: bool, perturb: float,
+                 u_perturb: Optional[Tensor]) -> Tensor:
+    """Coarse depths (models/rendering.py:216-232)."""
+    near, far = rays[:, 6:7], rays[:, 7:8]
+    t = torch.linspace(0, 1, n_samples)
+    if use_disp:
+        z = 1 / (1 / near * (1 - t) + 1 / far * t)
+    else:
+        z = near * (1 - t) + far * t
+    z = z.expand(rays.shape[0], n_samples)
+    if perturb > 0:
+        mid = 0.5 * (z[:, :-1] + z[:, 1:])
+        hi = torch.cat([mid, z[:, -1:]], -1)
+        lo = torch.cat([z[:, :1], mid], -1)
+        z = lo + (hi - lo) * (perturb * u_perturb)
+    return z
+
+
+def composite(sigmas: Tensor, rgbs: Optional[Tensor], z: Tensor, dirs: Tensor,
+              noise: Optional[Tensor], noise_std: float, white_back: bool):
+    """Volume-rendering integral (models/rendering.py:170-198; disp from
+    rendering_shadows.py:198 / rendering_rgb_sm.py:197).
+
+    Returns dict(weights, opacity, depth, disp[, rgb]).
+    """
+    delta = z[:, 1:] - z[:, :-1]
+    delta = torch.cat([delta, torch.full_like(delta[:, :1], 1e10)], -1)
+    delta = delta * torch.norm(dirs.unsqueeze(1), dim=-1)
+    raw = sigmas if noise is None else sigmas + noise * noise_std
+    alpha = 1 - torch.exp(-delta * torch.relu(raw))
+    trans = torch.cumprod(torch.cat([torch.ones_like(alpha[:, :1]), 1 - alpha + 1e-10], -1), -1)[:, :-1]
+    w = alpha * trans
+    out = {"weights": w, "opacity": w.sum(1), "depth": (w * z).sum(-1)}
+    out["disp"] = 1.0 / torch.max(1e-10 * torch.ones_like(out["depth"]), out["depth"] / w.sum(-1))
+    if rgbs is not None:
+        rgb = (w.unsqueeze(-1) * rgbs).sum(-2)
+        if white_back:
+            rgb = rgb + 1 - out["opacity"].unsqueeze(-1)
+        out["rgb"] = rgb
+    return out
+
+
+def pdf_cdf(weights_mid: Tensor, eps: float = 1e-5) -> Tensor:
+    """cdf of sample_pdf (models/rendering.py:29-34): (N, n_bins+1), cdf[:,0]=0."""
+    w = weights_mid + eps
+    pdf = w / torch.sum(w, -1, keepdim=True)
+    cdf = torch.cumsum(pdf, -1)
+    return torch.cat([torch.zeros_like(cdf[:, :1]), cdf], -1)
+
+
+def searchsorted_rows(a: np.ndarray, v: np.ndarray, side: str = "left") -> np.ndarray:
+    """Row-wise searchsorted with 1-row broadcast, int64 result.
+
+    Semantics of torchsearchsorted (src/torchsearchsorted/searchsorted.py:20-53,
+    src/cpu/searchsorted_cpu_wrapper.cpp:41-122): result = number of a[row,:] that are
+    < v (side='left') or <= v (side='right').  The reference's own known-answer test
+    (torchsearchsorted/test/test_searchsorted.py:27-44) defines exactly this via
+    numpy.searchsorted, which is what we use."""
+    rows = max(a.shape[0], v.shape[0])
+    out = np.empty((rows, v.shape[1]), dtype=np.int64)
+    for r in range(rows):
+        ar = a[0] if a.shape[0] == 1 else a[r]
+        vr = v[0] if v.shape[0] == 1 else v[r]
+        out[r] = np.searchsorted(ar, vr, side=side)
+    return out
+
+
+def sample_pdf(rays: Tensor, weights_mid: Tensor, n_importance: int, u: Tensor, jitter: Tensor,
+               eps: float = 1e-5, return_index: bool = False):
+    """The fork's pixel-NeRF-style sampler (models/rendering.py:14-48): bin index by
+    upper-bound search in the cdf, second uniform jitter, linear map of
+    (index+jitter)/n_bins between near and far.  `det` is ignored by the reference."""
+    n_bins = weights_mid.shape[1]
+    cdf = pdf_cdf(weights_mid, eps)
+    idx = torch.searchsorted(cdf, u.contiguous(), right=True)
+    ind = torch.clamp_min(idx.float() - 1.0, 0.0)
+    t = (ind + jitter) / n_bins
+    near, far = rays[:, -2:-1], rays[:, -1:]
+    z = near * (1 - t) + far * t
+    if return_index:
+        return z, ind.long()
+    return z
+
+
+def render_rays(params: Sequence[Dict[str, Tensor]], rays: Tensor, *, n_samples: int = 64,
+                use_disp: bool = False, perturb: float = 0.0, noise_std: float = 1.0,
+                n_importance: int = 0, white_back: bool = False, test_time: bool = False,
+                variant: str = "rgb", noise: Optional[Dict[str, Tensor]] = None,
+                xyz_freqs: int = 10, dir_freqs: int = 4, D: int = 8, skips=(4,),
+                return_aux: bool = False) -> Dict[str, Tensor]:
+    """render_rays of the three reference variants.
+
+    variant='rgb'      models/rendering.py:84-272        keys rgb_*/depth_*/opacity_*
+    variant='depth'    models/rendering_shadows.py:94-281 sigma-only MLP, keys depth_*/opacity_*/disp_map_*
+    variant='rgb_sm'   models/rendering_rgb_sm.py:87-278  'rgb' + disp_map_*
+
+    `noise` holds the injected random tensors (see module docstring); an optional
+    key 'z_fine' overrides the output of sample_pdf (used to compare end to end with
+    bin flips excluded).
+    """
+    noise = noise or {}
+    in_xyz = 3 * (2 * xyz_freqs + 1)
+    N = rays.shape[0]
+    o, d = rays[:, 0:3], rays[:, 3:6]
+    dir_enc = embed(d, dir_freqs)
+    depth_only = variant == "depth"
+
+    def run_pass(p, z, nz, weights_only):
+        S = z.shape[1]
+        pts = (o.unsqueeze(1) + d.unsqueeze(1) * z.unsqueeze(2)).reshape(-1, 3)
+        x = embed(pts, xyz_freqs)
+        sig_only = weights_only or depth_only
+        if not sig_only:
+            x = torch.cat([x, torch.repeat_interleave(dir_enc, S, dim=0)], 1)
+        raw = mlp_forward(p, x, sigma_only=sig_only, D=D, skips=skips, in_xyz=in_xyz)
+        if sig_only:
+            sig, rgb = raw.view(N, S), None
+        else:
+            raw = raw.view(N, S, 4)
+            sig, rgb = raw[..., 3], raw[..., :3]
+        return composite(sig, rgb, z, d, nz, noise_std, white_back)
+
+    z = stratified_z(rays, n_samples, use_disp, perturb, noise.get("u_perturb"))
+    aux = {"z_coarse": z}
+    c = run_pass(params[0], z, noise.get("noise_coarse"), weights_only=test_time)
+    res: Dict[str, Tensor] = {}
+    if test_time:
+        res["opacity_coarse"] = c["opacity"]
+    else:
+        if not depth_only:
+            res["rgb_coarse"] = c["rgb"]
+        res["depth_coarse"] = c["depth"]
+        res["opacity_coarse"] = c["opacity"]
+        if variant in ("depth", "rgb_sm"):
+            res["disp_map_coarse"] = c["disp"]
+    aux["weights_coarse"] = c["weights"]
+    if n_importance > 0:
+        if "z_fine" in noise:
+            zf = noise["z_fine"]
+        else:
+            zf = sample_pdf(rays, c["weights"][:, 1:-1], n_importance,
+                            noise["u_fine"], noise["jitter_fine"]).detach()
+        aux["z_fine"] = zf
+        z2, _ = torch.sort(torch.cat([z, zf], -1), -1)
+        aux["z_all"] = z2
+        f = run_pass(params[1], z2, noise.get("noise_fine"), weights_only=False)
+        if not depth_only:
+            res["rgb_fine"] = f["rgb"]
+        res["depth_fine"] = f["depth"]
+        res["opacity_fine"] = f["opacity"]
+        if variant in ("depth", "rgb_sm"):
+            res["disp_map_fine"] = f["disp"]
+        aux["weights_fine"] = f["weights"]
+    if return_aux:
+        return res, aux
+    return res
+
+
+# ---------------------------------------------------------------------------
+# models/camera.py + models/efficient_shadow_mapping.py
+# ---------------------------------------------------------------------------
+
+SHADOW_EPS = 1e-5  # efficient_shadow_mapping.py:8, rendering_shadows.py:357
+
+
+def camera_matrix(hfov_deg: float, res: Tuple[int, int]) -> Tensor:
+    """3x3 planar-pinhole matrix with columns a,b,c (models/camera.py:20-31)."""
+    w, h = res
+    hf = torch.tensor(hfov_deg) / torch.tensor(180.0) * np.pi
+    a = torch.tensor([1.0, 0.0, 0.0])
+    b = torch.tensor([0.0, -1.0, 0.0])
+    c = torch.tensor([-w / 2.0, h / 2, -w / (2 * torch.tan(hf / 2.0))])
+    return torch.stack([a, b, c]).T
+
+
+def pose_camera(cam: Tensor, c2w: Tensor) -> Tuple[Tensor, Tensor]:
+    """(eye_pos, M) for a Blender c2w (3,4) (models/camera.py:69-89, non-transform branch)."""
+    return c2w[:, 3].float(), c2w[:, :3].float() @ cam.float()
+
+
+def transformation_to(cam_M: Tensor, cam_eye: Tensor, light_M: Tensor, light_eye: Tensor):
+    """R = ML^-1 MC, Q = ML^-1 (OC - OL) (models/camera.py:121-132)."""
+    inv = torch.inverse(light_M)
+    return inv @ cam_M, inv @ (cam_eye - light_eye)
+
+
+def normed_w(M: Tensor, pixel_depth: Tensor) -> Tensor:
+    """[i,j,1,depth] -> [i,j,1, depth/(|M [i,j,1]^T| + 1e-5)] (efficient_shadow_mapping.py:47-62)."""
+    pix = pixel_depth[:, :3]
+    coords = (pix[:, None, :] * M).sum(-1)
+    nrm = torch.linalg.norm(coords, dim=1) + SHADOW_EPS
+    return torch.cat([pix, (pixel_depth[:, 3] / nrm).view(-1, 1)], 1)
+
+
+def diff_projections(pix: Tensor, w_cam: Tensor, R: Tensor, Q: Tensor) -> Tensor:
+    """K=[ul,vl,wl] (efficient_shadow_mapping.py:65-83)."""
+    proj = (pix[:, None, :] * R).sum(-1)
+    uvw = w_cam[:, None] * proj + Q
+    wl = uvw[:, 2]
+    return torch.stack([uvw[:, 0] / wl, uvw[:, 1] / wl, wl], 1)
+
+
+def projected_depths(res: Tuple[int, int], K: Tensor, w_light: Tensor):
+    """clamp / truncate / gather (efficient_shadow_mapping.py:85-100).  Row index is vl."""
+    w, h = res
+    ul = K[:, 0].clamp(min=0.0).clamp(max=w - 1.0)
+    vl = K[:, 1].clamp(min=0.0).clamp(max=h - 1.0)
+    return K[:, 2], w_light.view(w, h)[vl.long(), ul.long()]
+
+
+def shadow_map(wl: Tensor, w_light_b: Tensor, mode: str, delta=1e-2, epsilon=0.0,
+               new_min=0.0, new_max=1.0, sigmoid=False) -> Tensor:
+    """efficient_shadow_mapping.py:103-130 (+ normalize_min_max :10-11)."""
+    diff = wl - w_light_b
+    if mode == "shadow_method_1":
+        diff = torch.max(diff / delta, torch.tensor(epsilon))
+    elif mode == "shadow_method_2":
+        diff = (diff - diff.min()) / (diff.max() - diff.min() + SHADOW_EPS) * (new_max - new_min) + new_min
+        if sigmoid:
+            diff = torch.sigmoid(diff)
+    else:
+        raise ValueError("{} not found".format(mode))
+    return torch.stack([diff, diff, diff], 1).clip(0.0, 1.0)
+
+
+def run_shadow_mapping(res, cam_M, cam_eye, light_M, light_eye, mesh_range_cam, normed_light,
+                       mode="shadow_method_1", **kw) -> Tensor:
+    """efficient_shadow_mapping.py:19-44 for one same-camera segment."""
+    wc = normed_w(cam_M, mesh_range_cam)
+    R, Q = transformation_to(cam_M, cam_eye, light_M, light_eye)
+    K = diff_projections(wc[:, :3], wc[:, 3], R, Q)
+    wl, wlb = projected_depths(res, K, normed_light[:, 3])
+    return shadow_map(wl, wlb, mode, **kw)
+
+
+def camera_segments(eye_pos: Tensor) -> List[Tuple[int, int]]:
+    """Consecutive same-eye_pos runs, as found by the Python loop at
+    rendering_shadows.py:385-406 (a new segment starts where eye_pos differs from the
+    eye_pos of the current segment's first ray)."""
+    n = eye_pos.shape[0]
+    segs, start = [], 0
+    for i in range(n):
+        if not torch.equal(eye_pos[start], eye_pos[i]):
+            segs.append((start, i))
+            start = i
+    segs.append((start, n))
+    return segs
+
+
+def efficient_sm(cam_pixels, light_pixels, cam_results, light_results, ppc, light_M, light_eye,
+                 image_shape, fine_sampling, light_n_importance, shadow_method,
+                 out_prefix: str = "rgb") -> Dict[str, Tensor]:
+    """rendering_shadows.py:359-482 (out_prefix='rgb') and its twin
+    rendering_rgb_sm.py:356-480 (out_prefix='sm')."""
+    eye, cams = ppc["eye_pos"], ppc["camera"]
+    segs = camera_segments(eye)
+
+    def run(cam_depth, light_depth):
+        mrc = torch.cat([cam_pixels, cam_depth.view(-1, 1)], 1)
+        nl = normed_w(light_M, torch.cat([light_pixels, light_depth.view(-1, 1)], 1))
+        outs = [run_shadow_mapping(image_shape, cams[s], eye[s], light_M, light_eye, mrc[s:e], nl,
+                                   mode=shadow_method) for (s, e) in segs]
+        return torch.cat(outs, 0).view(-1, 3) + SHADOW_EPS
+
+    cam_results[f"{out_prefix}_coarse"] = run(cam_results["depth_coarse"], light_results["depth_coarse"])
+    if fine_sampling:
+        ld = light_results["depth_fine"] if light_n_importance else light_results["depth_coarse"]
+        cam_results[f"{out_prefix}_fine"] = run(cam_results["depth_fine"], ld)
+    return cam_results
+
+
+# ---------------------------------------------------------------------------
+# Synthetic inputs.  Ray generation restates datasets/ray_utils.py:5-50.
+# ---------------------------------------------------------------------------
+
+def blender_rays(n: int, seed: int = 1, H: int = 800, W: int = 800, near: float = 2.0, far: float = 6.0,
+                 radius: float = 4.0, theta_deg: float = 30.0, phi_deg: float = -30.0) -> Tensor:
+    """(n,8) rays of a random pixel subset of one Blender-style view
+    (datasets/ray_utils.py:5-24 directions, :27-50 world rays, d normalised :43)."""
+    g = torch.Generator().manual_seed(seed)
+    focal = 0.5 * W / math.tan(0.5 * 0.6911112070083618)
+    pix = torch.randperm(H * W, generator=g)[:n]
+    i, j = (pix % W).float(), (pix // W).float()
+    dirs = torch.stack([(i - W / 2) / focal, -(j - H / 2) / focal, -torch.ones_like(i)], -1)
+    th, ph = math.radians(theta_deg), math.radians(phi_deg)
+    t_r = torch.tensor([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, radius], [0, 0, 0, 1.0]])
+    r_ph = torch.tensor([[1, 0, 0, 0], [0, math.cos(ph), -math.sin(ph), 0],
+                         [0, math.sin(ph), math.cos(ph), 0], [0, 0, 0, 1.0]])
+    r_th = torch.tensor([[math.cos(th), 0, -math.sin(th), 0], [0, 1, 0, 0],
+                         [math.sin(th), 0, math.cos(th), 0], [0, 0, 0, 1.0]])
+    flip = torch.tensor([[-1, 0, 0, 0], [0, 0, 1, 0], [0, 1, 0, 0], [0, 0, 0, 1.0]])
+    c2w = (flip @ r_th @ r_ph @ t_r)[:3, :4]
+    rd = dirs @ c2w[:, :3].T
+    rd = rd / torch.norm(rd, dim=-1, keepdim=True)
+    ro = c2w[:, 3].expand(rd.shape)
+    return torch.cat([ro, rd, near * torch.ones_like(ro[:, :1]), far * torch.ones_like(ro[:, :1])], 1).contiguous()
+
+
+def make_noise(n: int, nc: int, nf: int, seed: int = 2, perturb: bool = True) -> Dict[str, Tensor]:
+    """Random tensors in the reference's draw order."""
+    g = torch.Generator().manual_seed(seed)
+    out: Dict[str, Tensor] = {}
+    if perturb:
+        out["u_perturb"] = torch.rand(n, nc, generator=g)
+    out["noise_coarse"] = torch.randn(n, nc, generator=g)
+    if nf > 0:
+        out["u_fine"] = torch.rand(n, nf, generator=g)
+        out["jitter_fine"] = torch.rand(n, nf, generator=g)
+        out["noise_fine"] = torch.randn(n, nc + nf, generator=g)
+    return out

@@ -1,0 +1,139 @@
+"""Pin the CPU oracle (oracle/nerf_oracle.py) against outputs of the reference itself.
+
+The fixtures under tests/golden/ were produced by tests/make_golden.py, which imports
+/root/reference/models/*.py unmodified and injects the random tensors.  CPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nerf_oracle as O
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _case(npz, name):
+    pre = name + "/"
+    return {k[len(pre):]: npz[k] for k in npz.files if k.startswith(pre)}
+
+
+RENDER_CASES = [("rgb_train", "rgb"), ("rgb_test", "rgb"), ("rgb_disp_fork_bounds", "rgb"),
+                ("depth_train", "depth"), ("rgb_sm_train", "rgb_sm")]
+
+
+@pytest.mark.parametrize("name,variant", RENDER_CASES)
+def test_render_rays_matches_reference(name, variant):
+    c = _case(np.load(os.path.join(G, "render_rays.npz")), name)
+    N, Nc, Nf, W, use_disp, white_back, test_time = [int(v) for v in c["cfg"]]
+    perturb, noise_std, near, far = [float(v) for v in c["cfgf"]]
+    params = []
+    for s in (10, 11):
+        p = O.init_mlp_params(W=W, generator=torch.Generator().manual_seed(s))
+        params.append({k: v.requires_grad_() for k, v in p.items()})
+    noise = {k[len("noise_"):]: torch.from_numpy(v) for k, v in c.items() if k.startswith("noise_")}
+    res = O.render_rays(params, torch.from_numpy(c["rays"]), n_samples=Nc, use_disp=bool(use_disp),
+                        perturb=perturb, noise_std=noise_std, n_importance=Nf, white_back=bool(white_back),
+                        test_time=bool(test_time), variant=variant, noise=noise)
+    assert sorted(res.keys()) == list(c["keys"])
+    loss = 0
+    for k in res:
+        np.testing.assert_allclose(res[k].detach().numpy(), c["out_" + k], rtol=1e-6, atol=1e-7, err_msg=k)
+        loss = loss + (res[k] * torch.from_numpy(c["probe_" + k])).sum()
+    loss.backward()
+    for mi, p in enumerate(params):
+        for pn, pv in p.items():
+            g = pv.grad.numpy() if pv.grad is not None else np.zeros(pv.shape, np.float32)
+            ref = c[f"grad{mi}_{pn}"]
+            np.testing.assert_allclose(g, ref, rtol=1e-4, atol=1e-6 * max(1.0, np.abs(ref).max()), err_msg=f"{mi}/{pn}")
+
+
+def test_embedding_and_nerf_match_reference():
+    c = np.load(os.path.join(G, "nerf_modules.npz"))
+    x3 = torch.from_numpy(c["x3"])
+    assert np.array_equal(O.embed(x3, 10).numpy(), c["emb10"])
+    assert np.array_equal(O.embed(x3, 4).numpy(), c["emb4"])
+    assert np.array_equal(O.embed(x3, 4, logscale=False).numpy(), c["emb4_lin"])
+    p = O.init_mlp_params(generator=torch.Generator().manual_seed(20))
+    assert abs(float(sum(v.double().sum() for v in p.values())) - float(c["nerf256_wsum"][0])) < 1e-9
+    assert O.mlp_param_names() == list(c["nerf_keys"])
+    assert [str(tuple(p[k].shape)) for k in O.mlp_param_names()] == list(c["nerf_shapes"])
+    x90 = torch.from_numpy(c["x90"])
+    np.testing.assert_allclose(O.mlp_forward(p, x90).numpy(), c["nerf256_full"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(O.mlp_forward(p, x90[:, :63], sigma_only=True).numpy(), c["nerf256_sigma"],
+                               rtol=1e-6, atol=1e-7)
+
+
+def test_sample_pdf_matches_reference_bit_exact():
+    c = np.load(os.path.join(G, "sample_pdf.npz"))
+    z = O.sample_pdf(torch.from_numpy(c["rays"]), torch.from_numpy(c["w"]), c["u"].shape[1],
+                     torch.from_numpy(c["u"]), torch.from_numpy(c["jitter"]))
+    assert np.array_equal(z.numpy(), c["z"])
+
+
+def test_searchsorted_known_answers():
+    c = np.load(os.path.join(G, "searchsorted.npz"))
+    for i in range(int(c["n_cases"])):
+        for side in ("left", "right"):
+            out = O.searchsorted_rows(c[f"c{i}_a"], c[f"c{i}_v"], side)
+            assert out.dtype == np.int64 and np.array_equal(out, c[f"c{i}_{side}"])
+            # torch.searchsorted is what the depth-only variant calls (rendering_shadows.py:41)
+            if c[f"c{i}_a"].shape[0] == c[f"c{i}_v"].shape[0]:
+                t = torch.searchsorted(torch.from_numpy(c[f"c{i}_a"]), torch.from_numpy(c[f"c{i}_v"]),
+                                       right=(side == "right"))
+                assert np.array_equal(t.numpy(), out)
+    assert np.array_equal(O.searchsorted_rows(c["tie_a"], c["tie_v"], "right"), c["tie_right"])
+    assert np.array_equal(O.searchsorted_rows(c["tie_a"], c["tie_v"], "left"), c["tie_left"])
+
+
+def test_searchsorted_reference_extension_if_built():
+    """oracle/_ref/ holds the reference's own C++ searchsorted compiled from
+    /root/reference/torchsearchsorted/src/cpu (oracle/build_ref.py).  When present it must
+    agree with the restatement on the golden vectors."""
+    so = os.path.join(os.path.dirname(G), "..", "oracle", "_ref")
+    from oracle import ref_loader
+    ext = ref_loader.load_reference_searchsorted()
+    if ext is None:
+        pytest.skip("oracle/_ref not built")
+    c = np.load(os.path.join(G, "searchsorted.npz"))
+    for i in range(int(c["n_cases"])):
+        a, v = torch.from_numpy(c[f"c{i}_a"]), torch.from_numpy(c[f"c{i}_v"])
+        for side in ("left", "right"):
+            out = torch.empty(max(a.shape[0], v.shape[0]), v.shape[1], dtype=torch.long)
+            ext.searchsorted_cpu_wrapper(a, v, out, side == "left")
+            assert np.array_equal(out.numpy(), c[f"c{i}_{side}"])
+    a, v = torch.from_numpy(c["tie_a"]), torch.from_numpy(c["tie_v"])
+    out = torch.empty(1, v.shape[1], dtype=torch.long)
+    ext.searchsorted_cpu_wrapper(a, v, out, False)
+    assert np.array_equal(out.numpy(), c["tie_right"])
+
+
+@pytest.mark.parametrize("method", ["shadow_method_1", "shadow_method_2"])
+@pytest.mark.parametrize("lni", [0, 8])
+def test_efficient_sm_matches_reference(method, lni):
+    c = np.load(os.path.join(G, "shadow.npz"))
+    tag = f"{method}_lni{lni}"
+    t = lambda k: torch.from_numpy(c[k])
+    cd = {k: t(f"{tag}/cam_{k}").requires_grad_() for k in ("depth_coarse", "depth_fine")}
+    ld = {k: t(f"{tag}/light_{k}").requires_grad_() for k in ("depth_coarse", "depth_fine")}
+    out = O.efficient_sm(t("cam_pixels"), t("light_pixels"), dict(cd), dict(ld),
+                         {"eye_pos": t("eye_pos"), "camera": t("camera")}, t("light_camera"), t("light_eye"),
+                         tuple(int(v) for v in c["res"]), True, lni, method)
+    np.testing.assert_allclose(out["rgb_coarse"].detach().numpy(), c[f"{tag}/rgb_coarse"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(out["rgb_fine"].detach().numpy(), c[f"{tag}/rgb_fine"], rtol=1e-6, atol=1e-7)
+    probe = t(f"{tag}/probe")
+    ((out["rgb_coarse"] * probe).sum() + 2 * (out["rgb_fine"] * probe).sum()).backward()
+    for k in cd:
+        for grp, d in (("gcam", cd), ("glight", ld)):
+            g = d[k].grad.numpy() if d[k].grad is not None else np.zeros(d[k].shape, np.float32)
+            ref = c[f"{tag}/{grp}_{k}"]
+            np.testing.assert_allclose(g, ref, rtol=1e-4, atol=1e-6 * max(1.0, np.abs(ref).max()), err_msg=f"{grp}_{k}")
+
+
+def test_camera_algebra_matches_reference():
+    c = np.load(os.path.join(G, "shadow.npz"))
+    np.testing.assert_allclose(O.camera_matrix(30, (16, 16)).numpy(), c["cam_init_30_16"], rtol=1e-6)
+    R, Q = O.transformation_to(torch.from_numpy(c["cam0_M"]), torch.from_numpy(c["cam0_eye"]),
+                               torch.from_numpy(c["light_camera"]), torch.from_numpy(c["light_eye"]))
+    np.testing.assert_allclose(R.numpy(), c["R01"], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(Q.numpy(), c["Q01"], rtol=1e-6, atol=1e-7)
