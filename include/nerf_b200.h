@@ -1,0 +1,176 @@
+/* nerf_b200.h — C ABI of the B200-native nerf_pl ray-rendering hot path.
+ *
+ * One shared library (nerf_pl_b200/lib/libnerf_b200.so), sm_100a only, no CPU fallback.
+ * Every entry point:
+ *   - takes DEVICE pointers to contiguous row-major buffers (fp32 unless stated), plain sizes,
+ *     and the CUDA stream to launch on (a cudaStream_t passed as void*; NULL = legacy default);
+ *   - returns 0 on success, otherwise an NRF_ERR_* code; nrf_last_error() gives the text;
+ *   - is asynchronous w.r.t. the host (no device synchronisation inside).
+ *
+ * The reference (ktiwary2/nerf_pl @ 99d40cb) has no FFI of its own for this path except the
+ * torchsearchsorted extension; its "operator API" is the Python functions cited below.  Each
+ * entry point names the reference code it replaces (paths relative to the reference root).
+ */
+#ifndef NERF_B200_H_
+#define NERF_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NRF_OK 0
+#define NRF_ERR_INVALID 1     /* bad argument (shape, null pointer, unsupported size) */
+#define NRF_ERR_CUDA 2        /* a CUDA runtime call or launch failed */
+#define NRF_ERR_UNSUPPORTED 3 /* valid request this build cannot serve (e.g. W != 256 on the tensor-core path) */
+#define NRF_ERR_WORKSPACE 4   /* caller-provided workspace too small */
+
+#define NRF_MAX_D 16
+
+typedef void* nrf_stream_t;
+
+/* Library / device ------------------------------------------------------------------------- */
+int nrf_abi_version(void);
+const char* nrf_last_error(void);
+/* 0 iff the current device is compute capability 10.x (the only supported target). */
+int nrf_check_device(void);
+
+/* a4  stratified depth sampling — models/rendering.py:216-232
+ * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);
+ * u (N,n_samples) uniform [0,1) or NULL (required iff perturb > 0); z_out (N,n_samples). */
+int nrf_sample_coarse(const float* rays, const float* t_steps, int64_t n_rays, int n_samples,
+                      int use_disp, float perturb, const float* u, float* z_out, nrf_stream_t stream);
+
+/* a6  positional encoding — models/nerf.py:21-38 (Embedding.forward)
+ * x (rows,channels) -> out (rows, channels*(2*n_freqs+1)); freqs (n_freqs) device array. */
+int nrf_embed_fwd(const float* x, int64_t rows, int channels, const float* freqs, int n_freqs,
+                  float* out, nrf_stream_t stream);
+int nrf_embed_bwd(const float* x, const float* grad_out, int64_t rows, int channels, const float* freqs,
+                  int n_freqs, float* grad_x, nrf_stream_t stream);
+
+/* a10 alpha compositing — models/rendering.py:170-198 (+disp rendering_shadows.py:198)
+ * sigma (N,S); rgb (N,S,3) or NULL (depth-only / weights-only); z (N,S); rays (N,8);
+ * noise (N,S) or NULL.  Outputs: weights (N,S); rgb_out (N,3) or NULL; depth/opacity (N);
+ * disp_out (N) or NULL. */
+int nrf_composite_fwd(const float* sigma, const float* rgb, const float* z, const float* rays,
+                      const float* noise, float noise_std, int white_back, int64_t n_rays, int n_samples,
+                      float* weights_out, float* rgb_out, float* depth_out, float* opacity_out,
+                      float* disp_out, nrf_stream_t stream);
+/* Gradients of a scalar loss w.r.t. sigma (N,S) and rgb (N,S,3), given the gradients of the
+ * outputs (any of g_* may be NULL = zero).  g_weights (N,S) or NULL. */
+int nrf_composite_bwd(const float* sigma, const float* rgb, const float* z, const float* rays,
+                      const float* noise, float noise_std, int white_back, int64_t n_rays, int n_samples,
+                      const float* g_rgb, const float* g_depth, const float* g_opacity, const float* g_disp,
+                      const float* g_weights, float* d_sigma, float* d_rgb, nrf_stream_t stream);
+
+/* a11 hierarchical resampling — models/rendering.py:14-48 (sample_pdf as called at :253)
+ * weights_coarse (N,n_coarse): the FULL coarse weights; bins are weights[:,1:-1].
+ * u, jitter (N,n_importance).  z_fine_out (N,n_importance); idx_out (N,n_importance) int64 or
+ * NULL (clamped bin index); cdf_out (N,n_coarse-1) or NULL. */
+int nrf_sample_pdf(const float* rays, const float* weights_coarse, int64_t n_rays, int n_coarse,
+                   int n_importance, const float* u, const float* jitter, float eps, float* z_fine_out,
+                   int64_t* idx_out, float* cdf_out, nrf_stream_t stream);
+
+/* a13 sort(cat([z_coarse, z_fine])) per ray — models/rendering.py:257.  z_out (N,nc+nf). */
+int nrf_merge_sort(const float* z_coarse, const float* z_fine, int64_t n_rays, int nc, int nf,
+                   float* z_out, nrf_stream_t stream);
+
+/* a12 row-wise searchsorted — torchsearchsorted/src/cuda/searchsorted_cuda_kernel.cu:83-142,
+ * src/torchsearchsorted/searchsorted.py:20-53.  a (nrow_a,ncol_a) sorted rows, v (nrow_v,ncol_v),
+ * out (max(nrow_a,nrow_v), ncol_v) int64; one of nrow_a/nrow_v may be 1 (broadcast). */
+int nrf_searchsorted(const float* a, const float* v, int64_t* out, int64_t nrow_a, int64_t nrow_v,
+                     int64_t ncol_a, int64_t ncol_v, int side_left, nrf_stream_t stream);
+
+/* a8  NeRF MLP — models/nerf.py:41-124.  Parameters in the checkpoint layout
+ * (utils/__init__.py:55-76): weights (out,in) row-major fp32, biases (out). */
+typedef struct {
+  int32_t D, W, in_xyz, in_dir;
+  uint32_t skip_mask;                 /* bit i set <=> layer i concatenates the encoding first */
+  const float* xyz_w[NRF_MAX_D];
+  const float* xyz_b[NRF_MAX_D];
+  const float* final_w; const float* final_b;
+  const float* dir_w;   const float* dir_b;
+  const float* sigma_w; const float* sigma_b;
+  const float* rgb_w;   const float* rgb_b;
+} nrf_mlp_params;
+
+typedef struct {                      /* same shapes; gradients are ACCUMULATED (+=) */
+  float* xyz_w[NRF_MAX_D];
+  float* xyz_b[NRF_MAX_D];
+  float* final_w; float* final_b;
+  float* dir_w;   float* dir_b;
+  float* sigma_w; float* sigma_b;
+  float* rgb_w;   float* rgb_b;
+} nrf_mlp_grads;
+
+/* fp32 (parity) MLP.  Two input forms:
+ *   rays form     : points o+d*z are encoded on the fly (rendering.py:234, nerf.py:21-38):
+ *                   rays (N,8), z (N,S), rows = N*S, row r belongs to ray r/S.
+ *   embedded form : x (rows, in_xyz[+in_dir]) already encoded (NeRF.forward, nerf.py:83).
+ * sigma_out (rows); rgb_out (rows,3) or NULL when sigma_only.
+ * stash: workspace of >= nrf_mlp_fp32_workspace_bytes(...) bytes; with need_grad it holds the
+ * activations consumed by nrf_mlp_fp32_bwd. */
+size_t nrf_mlp_fp32_workspace_bytes(const nrf_mlp_params* p, int64_t rows, int64_t n_rays, int sigma_only,
+                                    int need_grad);
+int nrf_mlp_fp32_fwd_rays(const nrf_mlp_params* p, const float* rays, const float* z, int64_t n_rays,
+                          int n_samples, int xyz_freqs, int dir_freqs, int sigma_only, int need_grad,
+                          float* sigma_out, float* rgb_out, void* workspace, size_t workspace_bytes,
+                          nrf_stream_t stream);
+int nrf_mlp_fp32_fwd_embedded(const nrf_mlp_params* p, const float* x, int64_t rows, int sigma_only,
+                              int need_grad, float* sigma_out, float* rgb_out, void* workspace,
+                              size_t workspace_bytes, nrf_stream_t stream);
+/* d_sigma (rows), d_rgb (rows,3) or NULL; `rgb_out` is the forward output (sigmoid backward).
+ * x/n_rays/n_samples describe the same input form as the forward that filled `workspace`
+ * (x == NULL for the rays form). */
+int nrf_mlp_fp32_bwd(const nrf_mlp_params* p, const nrf_mlp_grads* g, const float* x, int64_t rows,
+                     int64_t n_rays, int n_samples, int sigma_only, const float* d_sigma, const float* d_rgb,
+                     const float* rgb_out, void* workspace, size_t workspace_bytes, nrf_stream_t stream);
+
+/* bf16 tensor-core (tcgen05/TMEM/TMA) MLP, D=8 W=256 L=(10,4) skips=[4] only.
+ * packed: device buffer of nrf_mlp_tc_packed_bytes() bytes filled by nrf_mlp_tc_pack(). */
+size_t nrf_mlp_tc_packed_bytes(void);
+int nrf_mlp_tc_pack(const nrf_mlp_params* p, void* packed, nrf_stream_t stream);
+size_t nrf_mlp_tc_stash_bytes(int64_t rows, int sigma_only);
+int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float* z, int64_t n_rays, int n_samples,
+                   int sigma_only, float* sigma_out, float* rgb_out, void* stash, size_t stash_bytes,
+                   nrf_stream_t stream);
+size_t nrf_mlp_tc_bwd_workspace_bytes(int64_t rows, int sigma_only);
+int nrf_mlp_tc_bwd(const void* packed, const nrf_mlp_grads* g, const float* rays, const float* z,
+                   int64_t n_rays, int n_samples, int sigma_only, const float* d_sigma, const float* d_rgb,
+                   const float* rgb_out, const void* stash, size_t stash_bytes, void* workspace,
+                   size_t workspace_bytes, nrf_stream_t stream);
+
+/* a14-a19 shadow test — models/efficient_shadow_mapping.py:19-130, models/camera.py:121-132,
+ * models/rendering_shadows.py:359-482 (segmentation by eye_pos :385-406).
+ * cam_pixels (n,3) [i+.5, j+.5, 1]; cam_depth (n); cam_M (n,3,3); cam_eye (n,3);
+ * light_Minv (3,3) = inverse(light.camera); light_M (3,3); light_eye (3);
+ * light_pixels (W*H,3); light_depth (W*H).  If light_M and light_pixels are both NULL,
+ * light_depth is taken as already normalised (the contract of run_shadow_mapping :29-30).
+ * mode: 1 = shadow_method_1, 2 = shadow_method_2.
+ * out (n,3) = clip(shadow,0,1) + out_bias.  workspace >= nrf_shadow_workspace_bytes(n, W*H). */
+size_t nrf_shadow_workspace_bytes(int64_t n, int64_t n_light);
+int nrf_shadow_fwd(const float* cam_pixels, const float* cam_depth, const float* cam_M, const float* cam_eye,
+                   const float* light_Minv, const float* light_M, const float* light_eye,
+                   const float* light_pixels, const float* light_depth, int64_t n, int res_w, int res_h,
+                   int mode, float delta, float epsilon, float new_min, float new_max, int sigmoid,
+                   float out_bias, float* out, void* workspace, size_t workspace_bytes, nrf_stream_t stream);
+/* g_out (n,3) -> g_cam_depth (n) (overwritten), g_light_depth (W*H) (ACCUMULATED, may be NULL). */
+int nrf_shadow_bwd(const float* cam_pixels, const float* cam_depth, const float* cam_M, const float* cam_eye,
+                   const float* light_Minv, const float* light_M, const float* light_eye,
+                   const float* light_pixels, const float* light_depth, int64_t n, int res_w, int res_h,
+                   int mode, float delta, float epsilon, float new_min, float new_max, int sigmoid,
+                   const float* g_out, float* g_cam_depth, float* g_light_depth, void* workspace,
+                   size_t workspace_bytes, nrf_stream_t stream);
+
+/* a14 get_normed_w — models/efficient_shadow_mapping.py:47-62.  pixel_depth (n,4) [i,j,1,depth], M (3,3).
+ * out (n,4) = [passthrough[:, :3], value[:,3] / (|M pixel_depth[:, :3]| + 1e-5)].  Forward: value =
+ * passthrough = pixel_depth.  Backward w.r.t. depth: value = passthrough = grad_out (linear map). */
+int nrf_normed_w(const float* pixel_depth, const float* value, const float* passthrough, const float* M,
+                 int64_t n, float* out, nrf_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERF_B200_H_ */

@@ -1,0 +1,41 @@
+// Shared helpers for the nerf_b200 CUDA translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include "../../include/nerf_b200.h"
+
+namespace nrf {
+
+void set_error(const char* fmt, ...);
+
+#define NRF_REQUIRE(cond, ...)                         \
+  do {                                                 \
+    if (!(cond)) {                                     \
+      ::nrf::set_error(__VA_ARGS__);                   \
+      return NRF_ERR_INVALID;                          \
+    }                                                  \
+  } while (0)
+
+#define NRF_CUDA(call)                                                                  \
+  do {                                                                                  \
+    cudaError_t e__ = (call);                                                           \
+    if (e__ != cudaSuccess) {                                                           \
+      ::nrf::set_error("%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+      return NRF_ERR_CUDA;                                                              \
+    }                                                                                   \
+  } while (0)
+
+#define NRF_LAUNCH_CHECK() NRF_CUDA(cudaGetLastError())
+
+static inline cudaStream_t as_stream(nrf_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+constexpr int kNumSMs = 148;  // B200
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace nrf

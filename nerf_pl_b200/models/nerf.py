@@ -1,0 +1,69 @@
+"""Embedding / NeRF with the reference's interface and checkpoint layout (models/nerf.py:4-124),
+computing through libnerf_b200.so.
+
+The parameter names (`xyz_encoding_{i}.0.{weight,bias}`, `xyz_encoding_final.*`,
+`dir_encoding.0.*`, `sigma.*`, `rgb.0.*`) are the checkpoint contract honoured by
+utils/__init__.py:55-76; `Embedding` owns no parameters or buffers."""
+import torch
+from torch import nn
+
+from .. import mlp as _mlp
+from .. import ops as _ops
+
+
+class Embedding(nn.Module):
+    def __init__(self, in_channels, N_freqs, logscale=True):
+        super().__init__()
+        self.N_freqs = N_freqs
+        self.in_channels = in_channels
+        self.funcs = [torch.sin, torch.cos]
+        self.out_channels = in_channels * (len(self.funcs) * N_freqs + 1)
+        if logscale:
+            self.freq_bands = 2 ** torch.linspace(0, N_freqs - 1, N_freqs)
+        else:
+            self.freq_bands = torch.linspace(1, 2 ** (N_freqs - 1), N_freqs)
+        self._dev_freqs = {}
+
+    def _freqs_on(self, device):
+        f = self._dev_freqs.get(device)
+        if f is None:
+            f = self.freq_bands.to(device=device, dtype=torch.float32).contiguous()
+            self._dev_freqs[device] = f
+        return f
+
+    def forward(self, x):
+        """x: (B, in_channels) CUDA fp32 -> (B, out_channels): [x, sin(f0 x), cos(f0 x), ...]."""
+        if not x.is_cuda:
+            raise RuntimeError("nerf_pl_b200.Embedding needs CUDA tensors (no CPU path)")
+        return _ops.embed(x, self._freqs_on(x.device))
+
+
+class NeRF(nn.Module):
+    def __init__(self, D=8, W=256, in_channels_xyz=63, in_channels_dir=27, skips=[4]):
+        super().__init__()
+        self.D, self.W = D, W
+        self.in_channels_xyz, self.in_channels_dir = in_channels_xyz, in_channels_dir
+        self.skips = skips
+        for i in range(D):
+            fan_in = in_channels_xyz if i == 0 else (W + in_channels_xyz if i in skips else W)
+            setattr(self, f"xyz_encoding_{i + 1}", nn.Sequential(nn.Linear(fan_in, W), nn.ReLU(True)))
+        self.xyz_encoding_final = nn.Linear(W, W)
+        self.dir_encoding = nn.Sequential(nn.Linear(W + in_channels_dir, W // 2), nn.ReLU(True))
+        self.sigma = nn.Linear(W, 1)
+        self.rgb = nn.Sequential(nn.Linear(W // 2, 3), nn.Sigmoid())
+        self._spec = _ops.MlpSpec(D, W, in_channels_xyz, in_channels_dir, skips)
+
+    @property
+    def spec(self):
+        return self._spec
+
+    def ordered_parameters(self):
+        """Parameters in the order of spec.names (= state_dict order)."""
+        named = dict(self.named_parameters())
+        return [named[n] for n in self._spec.names]
+
+    def forward(self, x, sigma_only=False):
+        """x: (B, in_xyz[+in_dir]) encoded input -> (B,4) [rgb, sigma] or (B,1) sigma."""
+        if not x.is_cuda:
+            raise RuntimeError("nerf_pl_b200.NeRF needs CUDA tensors (no CPU path)")
+        return _mlp.MlpEmbedded.apply(x, self._spec, bool(sigma_only), *self.ordered_parameters())

@@ -1,0 +1,22 @@
+"""Drop-in for models/rendering_rgb_sm.py: rgb renderer + disp_map_* (reference :87-278) and the
+efficient_sm twin that writes sm_coarse / sm_fine (reference :356-480)."""
+from ._render import render_rays_impl, sample_pdf  # noqa: F401
+from ._shadow import efficient_sm_impl, get_K_impl
+
+__all__ = ['render_rays', 'efficient_sm']
+
+
+def render_rays(models, embeddings, rays, N_samples=64, use_disp=False, perturb=0, noise_std=1, N_importance=0,
+                chunk=1024 * 32, white_back=False, test_time=False, _inject=None):
+    return render_rays_impl("rgb_sm", models, embeddings, rays, N_samples, use_disp, perturb, noise_std,
+                            N_importance, chunk, white_back, test_time, _inject)
+
+
+def efficient_sm(cam_pixels, light_pixels, cam_results, light_results, ppc, light_ppc, image_shape, fine_sampling,
+                 Light_N_importance, shadow_method):
+    return efficient_sm_impl("sm", cam_pixels, light_pixels, cam_results, light_results, ppc, light_ppc, image_shape,
+                             fine_sampling, Light_N_importance, shadow_method)
+
+
+def get_K(cam_pixels, cam_results, ppc, light_camera, fine_sampling):
+    return get_K_impl(cam_pixels, cam_results, ppc, light_camera, fine_sampling)

@@ -1,0 +1,251 @@
+"""GPU parity of each C-ABI operator against the CPU oracle on the same seeded inputs.
+Tolerances: bit-exact for index / sort / sampling arithmetic; 1e-5 relative for compositing
+(north_star); stated per test otherwise."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nerf_oracle as O
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import __graft_entry__ as ge
+    ge.build()
+    from nerf_pl_b200 import _lib
+    _lib.check(_lib.load().nrf_check_device(), "nrf_check_device")
+    return torch.device("cuda:0")
+
+
+def _rays(n, near=2.0, far=6.0, seed=1, unnorm=False):
+    r = O.blender_rays(n, seed=seed, near=near, far=far)
+    if unnorm:
+        r[:, 3:6] *= 1.7
+    return r
+
+
+@pytest.mark.parametrize("use_disp,perturb,near,far", [(False, 0.0, 2.0, 6.0), (False, 1.0, 2.0, 6.0),
+                                                       (True, 0.5, 1.0, 200.0), (False, 1.0, 0.0, 1.0)])
+@pytest.mark.parametrize("S", [64, 17])
+def test_sample_coarse_bit_exact(dev, use_disp, perturb, near, far, S):
+    from nerf_pl_b200 import ops
+    N = 777
+    rays = _rays(N, near, far)
+    u = torch.rand(N, S, generator=torch.Generator().manual_seed(5))
+    ref = O.stratified_z(rays, S, use_disp, perturb, u)
+    got = ops.sample_coarse(rays.to(dev), S, use_disp, perturb, u.to(dev), t_steps=torch.linspace(0, 1, S).to(dev))
+    assert torch.equal(got.cpu(), ref)
+
+
+def test_searchsorted_golden_and_reference_contract(dev):
+    from nerf_pl_b200 import ops
+    c = np.load(os.path.join(G, "searchsorted.npz"))
+    for i in range(int(c["n_cases"])):
+        a, v = torch.from_numpy(c[f"c{i}_a"]).to(dev), torch.from_numpy(c[f"c{i}_v"]).to(dev)
+        for side in ("left", "right"):
+            out = ops.searchsorted(a, v, side=side)
+            assert out.dtype == torch.long
+            assert np.array_equal(out.cpu().numpy(), c[f"c{i}_{side}"])
+    a, v = torch.from_numpy(c["tie_a"]).to(dev), torch.from_numpy(c["tie_v"]).to(dev)
+    assert np.array_equal(ops.searchsorted(a, v, side="right").cpu().numpy(), c["tie_right"])
+    assert np.array_equal(ops.searchsorted(a, v, side="left").cpu().numpy(), c["tie_left"])
+    out = torch.empty(1, 6, dtype=torch.long, device=dev)
+    assert ops.searchsorted(a, v, out, side="left") is out            # the `out=` form (test_searchsorted.py:22-25)
+    with pytest.raises(AssertionError):
+        ops.searchsorted(torch.zeros(3, 4, device=dev), torch.zeros(2, 4, device=dev))
+
+
+def test_searchsorted_random_vs_numpy(dev):
+    # the reference's own test loop (test_searchsorted.py:27-44), one repeat per shape
+    from nerf_pl_b200 import ops
+    rng = np.random.RandomState(0)
+    for Ba, Bv in [(1, 1), (1, 100), (100, 1), (200, 200)]:
+        for A in (1, 50, 500):
+            for V in (1, 12, 120):
+                a = np.sort(rng.rand(Ba, A).astype(np.float32), 1)
+                v = rng.rand(Bv, V).astype(np.float32)
+                for side in ("left", "right"):
+                    got = ops.searchsorted(torch.from_numpy(a).to(dev), torch.from_numpy(v).to(dev), side=side)
+                    assert np.array_equal(got.cpu().numpy(), O.searchsorted_rows(a, v, side))
+
+
+def test_sample_pdf_golden_and_bit_exact_given_cdf(dev):
+    from nerf_pl_b200 import ops
+    c = np.load(os.path.join(G, "sample_pdf.npz"))
+    rays, w = torch.from_numpy(c["rays"]), torch.from_numpy(c["w"])
+    u, jit = torch.from_numpy(c["u"]), torch.from_numpy(c["jitter"])
+    full = torch.nn.functional.pad(w, (1, 1))
+    z, idx, cdf = ops.sample_pdf(rays.to(dev), full.to(dev), u.shape[1], u.to(dev), jit.to(dev),
+                                 return_index=True, return_cdf=True)
+    # (i) bin indices are bit-exact given the identical cdf (north_star criterion 1)
+    ref_idx = torch.clamp_min(torch.searchsorted(cdf.cpu(), u, right=True) - 1, 0)
+    assert torch.equal(idx.cpu(), ref_idx)
+    # (ii) against the reference's own output: identical wherever the device cdf equals the CPU cdf
+    ref_cdf = O.pdf_cdf(w)
+    same_row = (cdf.cpu() == ref_cdf).all(1)
+    assert same_row.float().mean() > 0.5, "normaliser sum order should rarely change the cdf"
+    assert np.array_equal(z.cpu().numpy()[same_row.numpy()], c["z"][same_row.numpy()])
+    np.testing.assert_allclose(cdf.cpu().numpy(), ref_cdf.numpy(), rtol=0, atol=2.5e-7)
+    flips = (z.cpu() != torch.from_numpy(c["z"])).float().mean().item()
+    assert flips < 0.01, f"bin flip rate {flips}"
+
+
+@pytest.mark.parametrize("nc,nf", [(64, 64), (64, 128), (16, 24), (5, 0), (1, 1)])
+def test_merge_sort_bit_exact(dev, nc, nf):
+    from nerf_pl_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    zc = torch.sort(torch.rand(301, nc, generator=g) * 4 + 2, -1)[0]
+    zf = torch.rand(301, nf, generator=g) * 4 + 2
+    if nf > 2:
+        zf[:, 0] = zc[:, 0]                       # ties
+    ref = torch.sort(torch.cat([zc, zf], -1), -1)[0]
+    got = ops.merge_sort(zc.to(dev), zf.to(dev))
+    assert torch.equal(got.cpu(), ref)
+    assert bool((got[:, 1:] >= got[:, :-1]).all())
+
+
+def _composite_case(N, S, seed, with_rgb=True, near=2.0, far=6.0):
+    g = torch.Generator().manual_seed(seed)
+    rays = _rays(N, near, far, unnorm=True)
+    z = torch.sort(torch.rand(N, S, generator=g) * (far - near) + near, -1)[0]
+    sigma = torch.randn(N, S, generator=g) * 3
+    sigma[0] = -1.0                                # empty ray: opacity 0 -> disp NaN in the reference
+    sigma[1] = 50.0                                # opaque from the first sample
+    rgb = torch.rand(N, S, 3, generator=g) if with_rgb else None
+    noise = torch.randn(N, S, generator=g)
+    return rays, z, sigma, rgb, noise
+
+
+@pytest.mark.parametrize("S,with_rgb,white_back,noise_std", [(64, True, True, 1.0), (128, True, False, 0.0),
+                                                             (192, False, False, 1.0), (37, True, True, 0.5)])
+def test_composite_forward_1e5(dev, S, with_rgb, white_back, noise_std):
+    from nerf_pl_b200 import ops
+    rays, z, sigma, rgb, noise = _composite_case(515, S, 11, with_rgb)
+    ref = O.composite(sigma, rgb, z, rays[:, 3:6], noise, noise_std, white_back)
+    t = lambda x: None if x is None else x.to(dev)
+    got = ops.composite(t(sigma), t(rgb), t(z), t(rays), t(noise), noise_std, white_back)
+    for k in ("weights", "opacity", "depth") + (("rgb",) if with_rgb else ()):
+        np.testing.assert_allclose(got[k].cpu().numpy(), ref[k].numpy(), rtol=1e-5, atol=1e-6, err_msg=k)
+    d_ref, d_got = ref["disp"].numpy(), got["disp"].cpu().numpy()
+    assert np.array_equal(np.isnan(d_ref), np.isnan(d_got))
+    ok = ~np.isnan(d_ref)
+    np.testing.assert_allclose(d_got[ok], d_ref[ok], rtol=2e-5)
+
+
+@pytest.mark.parametrize("S,with_rgb,white_back", [(64, True, True), (128, True, False), (192, False, False),
+                                                   (37, True, True)])
+def test_composite_backward_matches_autograd(dev, S, with_rgb, white_back):
+    from nerf_pl_b200 import ops
+    N = 257
+    rays, z, sigma, rgb, noise = _composite_case(N, S, 13, with_rgb)
+    sigma[0] = torch.randn(S) * 3                 # keep disp finite everywhere for the gradient check
+    sigma[0, 0] = 2.0
+    sigma = sigma.requires_grad_()
+    if with_rgb:
+        rgb = rgb.requires_grad_()
+    ref = O.composite(sigma, rgb, z, rays[:, 3:6], noise, 1.0, white_back)
+    g = torch.Generator().manual_seed(17)
+    probes = {k: torch.rand(ref[k].shape, generator=g) for k in ("depth", "opacity", "disp") + (("rgb",) if with_rgb else ())}
+    sum((ref[k] * probes[k]).sum() for k in probes).backward()
+    t = lambda x: None if x is None else x.detach().to(dev)
+    d_sigma, d_rgb = ops.composite_bwd(t(sigma), t(rgb), t(z), t(rays), t(noise), 1.0, white_back,
+                                       t(probes.get("rgb")), t(probes["depth"]), t(probes["opacity"]), t(probes["disp"]))
+    gs = sigma.grad.numpy()
+    scale = np.abs(gs).max(1, keepdims=True) + 1e-12
+    assert np.max(np.abs(d_sigma.cpu().numpy() - gs) / scale) < 2e-4       # relative to the ray's largest gradient
+    if with_rgb:
+        np.testing.assert_allclose(d_rgb.cpu().numpy(), rgb.grad.numpy(), rtol=1e-5, atol=1e-7)
+
+
+def test_embedding_matches_reference_golden(dev):
+    from nerf_pl_b200.models.nerf import Embedding
+    c = np.load(os.path.join(G, "nerf_modules.npz"))
+    x = torch.from_numpy(c["x3"]).to(dev)
+    for key, emb in (("emb10", Embedding(3, 10)), ("emb4", Embedding(3, 4)), ("emb4_lin", Embedding(3, 4, logscale=False))):
+        got = emb(x).cpu().numpy()
+        # sin/cos of up to 1e5 rad: CUDA sinf/cosf are within 2 ulp of the correctly rounded value
+        np.testing.assert_allclose(got, c[key], rtol=0, atol=3e-7, err_msg=key)
+    xg = x.clone().requires_grad_()
+    out = Embedding(3, 4)(xg)
+    probe = torch.rand(out.shape, generator=torch.Generator().manual_seed(1)).to(dev)
+    (out * probe).sum().backward()
+    xc = torch.from_numpy(c["x3"]).requires_grad_()
+    (O.embed(xc, 4) * probe.cpu()).sum().backward()
+    np.testing.assert_allclose(xg.grad.cpu().numpy(), xc.grad.numpy(), rtol=1e-4, atol=1e-4)
+
+
+def test_nerf_forward_matches_reference_golden_fp32(dev):
+    from nerf_pl_b200.models.nerf import NeRF
+    c = np.load(os.path.join(G, "nerf_modules.npz"))
+    p = O.init_mlp_params(generator=torch.Generator().manual_seed(20))
+    m = NeRF().to(dev)
+    m.load_state_dict(p)
+    x = torch.from_numpy(c["x90"]).to(dev)
+    with torch.no_grad():
+        np.testing.assert_allclose(m(x).cpu().numpy(), c["nerf256_full"], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(m(x[:, :63].contiguous(), sigma_only=True).cpu().numpy(), c["nerf256_sigma"],
+                                   rtol=1e-5, atol=1e-6)
+
+
+def test_nerf_embedded_backward_fp32(dev):
+    from nerf_pl_b200.models.nerf import NeRF
+    g = torch.Generator().manual_seed(2)
+    p = O.init_mlp_params(D=4, W=64, skips=(2,), generator=g)
+    x = torch.randn(300, 90, generator=g)
+    pr = {k: v.clone().requires_grad_() for k, v in p.items()}
+    probe = torch.rand(300, 4, generator=g)
+    (O.mlp_forward(pr, x, D=4, skips=(2,)) * probe).sum().backward()
+    m = NeRF(D=4, W=64, skips=[2]).to(dev)
+    m.load_state_dict(p)
+    (m(x.to(dev)) * probe.to(dev)).sum().backward()
+    for n, t in m.named_parameters():
+        ref = pr[n].grad.numpy()
+        np.testing.assert_allclose(t.grad.cpu().numpy(), ref, rtol=1e-3, atol=1e-5 * max(1.0, np.abs(ref).max()), err_msg=n)
+
+
+@pytest.mark.parametrize("method", ["shadow_method_1", "shadow_method_2"])
+@pytest.mark.parametrize("lni", [0, 8])
+def test_efficient_sm_matches_reference_golden(dev, method, lni):
+    from nerf_pl_b200.models.camera import Camera
+    from nerf_pl_b200.models import rendering_rgb_sm, rendering_shadows
+    c = np.load(os.path.join(G, "shadow.npz"))
+    tag = f"{method}_lni{lni}"
+    t = lambda k: torch.from_numpy(c[k]).to(dev)
+    cd = {k: t(f"{tag}/cam_{k}").requires_grad_() for k in ("depth_coarse", "depth_fine")}
+    ld = {k: t(f"{tag}/light_{k}").requires_grad_() for k in ("depth_coarse", "depth_fine")}
+    light = Camera.from_camera_eyepos(torch.from_numpy(c["light_eye"]), torch.from_numpy(c["light_camera"]))
+    ppc = {"eye_pos": torch.from_numpy(c["eye_pos"]), "camera": torch.from_numpy(c["camera"])}
+    res = tuple(int(v) for v in c["res"])
+    out = rendering_shadows.efficient_sm(torch.from_numpy(c["cam_pixels"]), torch.from_numpy(c["light_pixels"]),
+                                         dict(cd), dict(ld), ppc, light, res, True, lni, method)
+    np.testing.assert_allclose(out["rgb_coarse"].detach().cpu().numpy(), c[f"{tag}/rgb_coarse"], rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(out["rgb_fine"].detach().cpu().numpy(), c[f"{tag}/rgb_fine"], rtol=1e-4, atol=2e-5)
+    probe = t(f"{tag}/probe")
+    ((out["rgb_coarse"] * probe).sum() + 2 * (out["rgb_fine"] * probe).sum()).backward()
+    for k in cd:
+        for grp, d in (("gcam", cd), ("glight", ld)):
+            g = d[k].grad.cpu().numpy() if d[k].grad is not None else np.zeros(d[k].shape, np.float32)
+            ref = c[f"{tag}/{grp}_{k}"]
+            np.testing.assert_allclose(g, ref, rtol=2e-3, atol=2e-4 * max(1.0, np.abs(ref).max()), err_msg=f"{grp}_{k}")
+    out2 = rendering_rgb_sm.efficient_sm(torch.from_numpy(c["cam_pixels"]), torch.from_numpy(c["light_pixels"]),
+                                         {k: v.detach() for k, v in cd.items()}, {k: v.detach() for k, v in ld.items()},
+                                         ppc, light, res, True, lni, method)
+    assert torch.equal(out2["sm_coarse"], out["rgb_coarse"].detach())
+
+
+def test_cpu_tensor_and_bad_mode_raise(dev):
+    from nerf_pl_b200 import ops
+    with pytest.raises(RuntimeError):
+        ops.sample_coarse(torch.zeros(4, 8), 8, False, 0.0)
+    with pytest.raises(RuntimeError):
+        ops.sample_pdf(torch.zeros(4, 8, device=dev), torch.zeros(4, 2, device=dev), 4, torch.zeros(4, 4, device=dev),
+                       torch.zeros(4, 4, device=dev))       # n_coarse < 3
+    # empty batch is a no-op, like slicing an empty chunk in the reference
+    assert ops.sample_coarse(torch.zeros(0, 8, device=dev), 8, False, 0.0).shape == (0, 8)

@@ -1,0 +1,141 @@
+"""End-to-end parity of render_rays (three variants) on the GPU: against the golden fixtures
+produced by the reference itself (W=64 models, fp32 mode) and against the oracle at full width
+(W=256; fp32 mode 1e-5-class, bf16 tensor-core mode 2e-3-class tolerances as stated below)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nerf_oracle as O
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import __graft_entry__ as ge
+    ge.build()
+    return torch.device("cuda:0")
+
+
+def _case(npz, name):
+    pre = name + "/"
+    return {k[len(pre):]: npz[k] for k in npz.files if k.startswith(pre)}
+
+
+def _models(params, dev, **kw):
+    from nerf_pl_b200.models.nerf import NeRF
+    ms = []
+    for p in params:
+        m = NeRF(**kw).to(dev)
+        m.load_state_dict(p)
+        ms.append(m)
+    return ms
+
+
+def _module_for(variant):
+    from nerf_pl_b200.models import rendering, rendering_rgb_sm, rendering_shadows
+    return {"rgb": rendering, "depth": rendering_shadows, "rgb_sm": rendering_rgb_sm}[variant]
+
+
+CASES = [("rgb_train", "rgb"), ("rgb_test", "rgb"), ("rgb_disp_fork_bounds", "rgb"), ("depth_train", "depth"),
+         ("rgb_sm_train", "rgb_sm")]
+
+
+@pytest.mark.parametrize("name,variant", CASES)
+def test_render_rays_vs_reference_golden_fp32(dev, name, variant):
+    import nerf_pl_b200
+    from nerf_pl_b200.models.nerf import Embedding
+    nerf_pl_b200.set_mlp_precision("fp32")
+    c = _case(np.load(os.path.join(G, "render_rays.npz")), name)
+    N, Nc, Nf, W, use_disp, white_back, test_time = [int(v) for v in c["cfg"]]
+    perturb, noise_std, near, far = [float(v) for v in c["cfgf"]]
+    params = [O.init_mlp_params(W=W, generator=torch.Generator().manual_seed(s)) for s in (10, 11)]
+    models = _models(params, dev, W=W)
+    inj = {k[len("noise_"):]: torch.from_numpy(v).to(dev) for k, v in c.items() if k.startswith("noise_")}
+    res = _module_for(variant).render_rays(models, [Embedding(3, 10), Embedding(3, 4)], torch.from_numpy(c["rays"]).to(dev),
+                                           Nc, bool(use_disp), perturb, noise_std, Nf, 1024 * 32, bool(white_back),
+                                           bool(test_time), _inject=inj)
+    assert sorted(res.keys()) == list(c["keys"])
+    loss = 0
+    for k in res:
+        ref = c["out_" + k]
+        # fp32 mode criterion: 1e-5 (relative to the key's range; depth reaches `far`)
+        np.testing.assert_allclose(res[k].detach().cpu().numpy(), ref, rtol=1e-5, atol=1e-5 * max(1.0, np.abs(ref).max()),
+                                   err_msg=k)
+        loss = loss + (res[k] * torch.from_numpy(c["probe_" + k]).to(dev)).sum()
+    if not test_time:
+        loss.backward()
+        for mi, m in enumerate(models):
+            for pn, pv in m.named_parameters():
+                ref = c[f"grad{mi}_{pn}"]
+                got = pv.grad.cpu().numpy() if pv.grad is not None else np.zeros_like(ref)
+                denom = np.linalg.norm(ref) + 1e-12
+                rel = np.linalg.norm(got - ref) / denom if np.linalg.norm(ref) > 0 else np.linalg.norm(got)
+                assert rel < 1e-4, f"grad {mi}/{pn}: relative L2 error {rel:.2e}"      # fp32 mode: <= 1e-4
+
+
+def _full_width_case(dev, precision, variant, N, Nc, Nf, near, far, use_disp, test_time, seed):
+    import nerf_pl_b200
+    from nerf_pl_b200.models.nerf import Embedding
+    nerf_pl_b200.set_mlp_precision(precision)
+    params = [O.init_mlp_params(generator=torch.Generator().manual_seed(s)) for s in (0, 1)]
+    for p in params:
+        for k in p:
+            p[k].requires_grad_()
+    rays = O.blender_rays(N, seed=seed, near=near, far=far)
+    perturb, noise_std = (0.0, 0.0) if test_time else (1.0, 1.0)
+    noise = O.make_noise(N, Nc, Nf, seed=seed + 1, perturb=perturb > 0)
+    ref, aux = O.render_rays(params, rays, n_samples=Nc, use_disp=use_disp, perturb=perturb, noise_std=noise_std,
+                             n_importance=Nf, white_back=True, test_time=test_time, variant=variant, noise=noise,
+                             return_aux=True)
+    models = _models([{k: v.detach() for k, v in p.items()} for p in params], dev)
+    inj = {k: v.to(dev) for k, v in noise.items()}
+    inj["z_fine"] = aux["z_fine"].to(dev)          # bin flips excluded: the fine depths are injected (SURVEY §8c iii)
+    got = _module_for(variant).render_rays(models, [Embedding(3, 10), Embedding(3, 4)], rays.to(dev), Nc, use_disp,
+                                           perturb, noise_std, Nf, 1024 * 32, True, test_time, _inject=inj)
+    return params, models, ref, got, aux, inj, rays
+
+
+@pytest.mark.parametrize("variant,near,far,use_disp,test_time", [("rgb", 2.0, 6.0, False, False),
+                                                                 ("rgb", 2.0, 6.0, False, True),
+                                                                 ("depth", 1.0, 200.0, True, False)])
+def test_full_width_fp32_vs_oracle(dev, variant, near, far, use_disp, test_time):
+    params, models, ref, got, *_ = _full_width_case(dev, "fp32", variant, 128, 64, 64, near, far, use_disp, test_time, 21)
+    assert sorted(got) == sorted(ref)
+    loss_r = loss_g = 0
+    g = torch.Generator().manual_seed(5)
+    for k in sorted(ref):
+        r = ref[k].detach().numpy()
+        np.testing.assert_allclose(got[k].detach().cpu().numpy(), r, rtol=2e-5, atol=1e-5 * max(1.0, np.abs(r).max()), err_msg=k)
+        pr = torch.rand(ref[k].shape, generator=g)
+        loss_r = loss_r + (ref[k] * pr).sum()
+        loss_g = loss_g + (got[k] * pr.to(got[k].device)).sum()
+    if not test_time and variant == "rgb":
+        loss_r.backward()
+        loss_g.backward()
+        for mi, m in enumerate(models):
+            for pn, pv in m.named_parameters():
+                r = params[mi][pn].grad.numpy()
+                rel = np.linalg.norm(pv.grad.cpu().numpy() - r) / (np.linalg.norm(r) + 1e-12)
+                assert rel < 1e-4, f"grad {mi}/{pn}: relative L2 error {rel:.2e}"
+
+
+def test_sample_pdf_flip_rate_end_to_end_fp32(dev):
+    """Without injecting z_fine the only end-to-end difference source is a bin flip when u lands
+    within an ulp-scale distance of a cdf entry; report and bound the rate."""
+    from nerf_pl_b200 import ops
+    params, models, ref, got, aux, inj, rays = _full_width_case(dev, "fp32", "rgb", 256, 64, 64, 2.0, 6.0, False, False, 31)
+    from nerf_pl_b200.mlp import forward_rays
+    z = aux["z_coarse"].to(dev)
+    sigma, rgb, _ = forward_rays(models[0].spec, [p.detach() for p in models[0].ordered_parameters()], rays.to(dev), z,
+                                 False, False, "fp32")
+    c = ops.composite(sigma, rgb, z, rays.to(dev), inj["noise_coarse"], 1.0, True)
+    zf = ops.sample_pdf(rays.to(dev), c["weights"], 64, inj["u_fine"], inj["jitter_fine"])
+    flips = (zf.cpu() != aux["z_fine"]).float().mean().item()
+    print(f"end-to-end fine-sample flip rate: {flips:.2e}")
+    assert flips < 2e-3
