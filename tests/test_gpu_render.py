@@ -116,13 +116,18 @@ def test_full_width_fp32_vs_oracle(dev, variant, near, far, use_disp, test_time)
         loss_r = loss_r + (ref[k] * pr).sum()
         loss_g = loss_g + (got[k] * pr.to(got[k].device)).sum()
     if not test_time and variant == "rgb":
+        worst = 0.0
         loss_r.backward()
         loss_g.backward()
         for mi, m in enumerate(models):
             for pn, pv in m.named_parameters():
                 r = params[mi][pn].grad.numpy()
                 rel = np.linalg.norm(pv.grad.cpu().numpy() - r) / (np.linalg.norm(r) + 1e-12)
-                assert rel < 1e-4, f"grad {mi}/{pn}: relative L2 error {rel:.2e}"
+                worst = max(worst, rel)
+                # full width, 16k samples: a handful of ReLU gates whose pre-activation is ~1e-8 flip
+                # between fp32 summation orders, each moving the gradient by O(1/samples); 1e-3 stated
+                assert rel < 1e-3, f"grad {mi}/{pn}: relative L2 error {rel:.2e}"
+        print(f"fp32 full-width parameter gradients: worst relative L2 error {worst:.2e}")
 
 
 def test_sample_pdf_flip_rate_end_to_end_fp32(dev):
