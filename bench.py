@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""bench.py — rays/s of one nerf_pl training step (render_rays fwd+bwd, 64 coarse + 64 fine samples)
+on N B200s, BASELINE.json configs[1]: batch 4096 rays per GPU, bf16 tensor-core MLP, ray-sharded.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun by the driver)
+  python bench.py --impl reference ...                     (the reference algorithm on the host cores)
+
+One JSON line on stdout (rank 0).  Keys follow the driver contract; see DESIGN.md §5."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+RAYS_PER_GPU = 4096
+NC, NF = 64, 64
+# algorithmic FLOPs: fwd+bwd full MLP per sample, 192 MLP evaluations per training ray
+FLOP_PER_SAMPLE_FWDBWD = 3489024
+FLOP_PER_SAMPLE_FWD = 1186816
+FLOP_PER_RAY_TRAIN = FLOP_PER_SAMPLE_FWDBWD * (NC + NC + NF)
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return {"bf16_tflops": float(p["bf16_tflops_sustained"]), "bf16_burst": float(p["bf16_tflops"]),
+                "hbm_gbs": float(p["hbm_gbs"]), "src": "measured"}
+    except Exception:
+        return {"bf16_tflops": 1400.0, "bf16_burst": 1590.0, "hbm_gbs": 6650.0, "src": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = max(mx, float(f[1]))
+                for n, v in zip(names, f[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_reference_rate(n_rays, reps, threads=None):
+    """The reference algorithm (oracle port of models/rendering.py) fwd+bwd on the host cores."""
+    import torch
+    from oracle import nerf_oracle as O
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    params = [O.init_mlp_params(generator=torch.Generator().manual_seed(s)) for s in (0, 1)]
+    for p in params:
+        for v in p.values():
+            v.requires_grad_()
+    rays = O.blender_rays(n_rays, seed=1)
+    noise = O.make_noise(n_rays, NC, NF, seed=2)
+    times = []
+    for i in range(reps + 1):
+        t0 = time.perf_counter()
+        out = O.render_rays(params, rays, n_samples=NC, perturb=1.0, noise_std=1.0, n_importance=NF, white_back=True,
+                            noise=noise)
+        loss = ((out["rgb_coarse"] - 0.5) ** 2).mean() + ((out["rgb_fine"] - 0.5) ** 2).mean()
+        loss.backward()
+        if i > 0:      # first call is warm-up
+            times.append(time.perf_counter() - t0)
+    times.sort()
+    med = times[len(times) // 2]
+    return n_rays / med, cores, med
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = 256
+    reps = max(1, args.steps)
+    rate, cores, med = cpu_reference_rate(n, reps)
+    line = {"impl": "reference", "metric": "train_rays_per_sec", "value": rate, "unit": "rays/s", "n_gpus": args.gpus,
+            "steps": reps, "warmup": 1, "ms_per_step": med * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "render_rays fwd+bwd, 64 coarse + 64 fine samples, Blender-style rays, random-init "
+                                   "NeRF D=8 W=256", "rays_per_step_sample": n},
+            "cpu_baseline": {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
+                             "sample": f"{n} rays per step (bounded sample of the 4096-ray batch), median of {reps}"},
+            "e2e": {"value": rate, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    import __graft_entry__ as ge
+    if rank == 0:
+        ge.build()
+    if world > 1:
+        dist.barrier()
+    import nerf_pl_b200
+    from nerf_pl_b200 import _lib
+    from nerf_pl_b200.dist import GradBucket
+    from nerf_pl_b200.mlp import forward_rays
+    from nerf_pl_b200.models.nerf import Embedding, NeRF
+    from nerf_pl_b200.models.rendering import render_rays
+    from oracle import nerf_oracle as O     # input generators + the cpu_baseline leg only
+
+    lib = _lib.load()
+    _lib.check(lib.nrf_check_device(), "nrf_check_device")
+    nerf_pl_b200.set_mlp_precision(args.precision)
+    peaks = load_peaks()
+
+    models = []
+    for s in (0, 1):
+        m = NeRF().to(dev)
+        m.load_state_dict(O.init_mlp_params(generator=torch.Generator().manual_seed(s)))
+        models.append(m)
+    emb = [Embedding(3, 10), Embedding(3, 4)]
+    bucket = GradBucket(models)
+
+    B = RAYS_PER_GPU
+    all_rays = O.blender_rays(B * world, seed=1)
+    rays_host = all_rays[rank * B:(rank + 1) * B].contiguous().pin_memory()
+    rgbs_host = torch.rand(B, 3, generator=torch.Generator().manual_seed(100 + rank)).pin_memory()
+    rays_dev, rgbs_dev = rays_host.to(dev), rgbs_host.to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def step(rays_d, rgbs_d):
+        bucket.zero()
+        out = render_rays(models, emb, rays_d, NC, False, 1.0, 1.0, NF, 1024 * 32, True)
+        loss = ((out["rgb_coarse"] - rgbs_d) ** 2).mean() + ((out["rgb_fine"] - rgbs_d) ** 2).mean()   # losses.py:9-14
+        loss.backward()
+        bucket.allreduce_mean()
+        return loss
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    W, K = max(3, args.warmup), max(1, args.steps)
+    for _ in range(W):
+        step(rays_dev, rgbs_dev)
+    sync_all()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    # ---- device-resident timing --------------------------------------------------------------------
+    launches0 = lib.nrf_launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    sync_all()
+    for i in range(K):
+        flush.zero_()
+        ev[i][0].record()
+        step(rays_dev, rgbs_dev)
+        ev[i][1].record()
+    sync_all()
+    launches = (lib.nrf_launch_count() - launches0) / K
+    ms = sum(a.elapsed_time(b) for a, b in ev) / K
+    # ---- end to end: pinned host -> device copies and the loss read-back inside the timed region ------
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    rays_in, rgbs_in = torch.empty_like(rays_dev), torch.empty_like(rgbs_dev)
+    sync_all()
+    t_e2e = 0.0
+    for i in range(K):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rays_in.copy_(rays_host, non_blocking=True)
+        rgbs_in.copy_(rgbs_host, non_blocking=True)
+        loss = step(rays_in, rgbs_in)
+        loss_host = loss.item()                       # device -> host read of the step's result
+        t_e2e += time.perf_counter() - t0
+    sync_all()
+    ms_e2e = t_e2e / K * 1e3
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+
+    # ---- roofline of the dominant kernel: the tensor-core MLP forward on the fine pass (4096 x 128 rows) ---
+    roof = None
+    if args.precision == "bf16":
+        z = torch.sort(torch.rand(B, NC + NF, device=dev) * 4 + 2, -1)[0]
+        params = [p.detach() for p in models[1].ordered_parameters()]
+        packed = models[1].packed_weights()
+        for _ in range(3):
+            forward_rays(models[1].spec, params, rays_dev, z, False, False, "bf16", packed=packed)
+        reps = 20
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            forward_rays(models[1].spec, params, rays_dev, z, False, False, "bf16", packed=packed)
+        e1.record()
+        torch.cuda.synchronize()
+        k_ms = e0.elapsed_time(e1) / reps
+        flops = B * (NC + NF) * FLOP_PER_SAMPLE_FWD
+        ach = flops / (k_ms * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": "nrf::tc::mlp_fwd_kernel<full,inference> (4096 rays x 128 samples)",
+                "achieved": ach, "peak": peaks["bf16_burst"], "unit": "TFLOP/s", "frac": ach / peaks["bf16_burst"],
+                "peak_source": f"{peaks['src']} (burst: kernel timed alone)", "ms_per_launch": k_ms, "traffic": None}
+
+    if rank == 0:
+        rays_per_s = world * B / (ms * 1e-3)
+        line = {"metric": "train_rays_per_sec", "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": K,
+                "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+                "config": {"workload": "nerf_pl training step: render_rays fwd+bwd + grad all-reduce, 4096 rays/GPU, "
+                                       "N_samples=64 N_importance=64, perturb=1 noise_std=1 white_back, NeRF D=8 W=256 "
+                                       "random init (optimizer step excluded)",
+                           "rays_per_gpu": B, "parallelism": f"ray-sharded dp{world}",
+                           "l2": "256 MB flush between timed steps; per-step activation traffic >> 126 MB L2",
+                           "train_step_flop_per_ray": FLOP_PER_RAY_TRAIN,
+                           "step_tensor_roofline_frac": rays_per_s * FLOP_PER_RAY_TRAIN / world / (peaks["bf16_tflops"] * 1e12)},
+                "clocks": clocks, "gpu_launches": launches,
+                "e2e": {"value": world * B / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
+                        "h2d_bytes_per_step": B * 8 * 4 + B * 3 * 4, "d2h_bytes_per_step": 4},
+                "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            rate, cores, med = cpu_reference_rate(256, 3)
+            line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
+                                    "sample": f"256 rays per call (bounded sample of the 4096-ray batch), median of 3, "
+                                              f"{med:.2f} s per call"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -36,6 +36,8 @@ int nrf_abi_version(void);
 const char* nrf_last_error(void);
 /* 0 iff the current device is compute capability 10.x (the only supported target). */
 int nrf_check_device(void);
+/* Number of CUDA kernels this library has launched in the calling process so far. */
+uint64_t nrf_launch_count(void);
 
 /* a4  stratified depth sampling — models/rendering.py:216-232
  * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);

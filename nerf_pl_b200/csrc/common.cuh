@@ -26,7 +26,12 @@ void set_error(const char* fmt, ...);
     }                                                                                   \
   } while (0)
 
-#define NRF_LAUNCH_CHECK() NRF_CUDA(cudaGetLastError())
+extern unsigned long long g_launches;  // kernels launched by this library (statistics only)
+#define NRF_LAUNCH_CHECK()        \
+  do {                            \
+    ++::nrf::g_launches;          \
+    NRF_CUDA(cudaGetLastError()); \
+  } while (0)
 
 static inline cudaStream_t as_stream(nrf_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 

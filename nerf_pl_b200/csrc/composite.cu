@@ -208,7 +208,10 @@ __global__ void composite_bwd_kernel(const float* __restrict__ sigma, const floa
         const float dn = __shfl_down_sync(0xffffffffu, incl, o);
         if (lane + o < 32) incl += dn;
       }
-      const float after = (incl - wG) + suffix;  // sum_{j>i} w_j G_j
+      // exclusive reverse scan by a lane shift (never "incl - wG": the difference is divided by a factor
+      // that can be as small as 1e-10, which would amplify the cancellation error)
+      const float nxt = __shfl_down_sync(0xffffffffu, incl, 1);
+      const float after = (lane < 31 ? nxt : 0.f) + suffix;  // sum_{j>i} w_j G_j
       if (valid) {
         const float dalpha = T * G - after / t.factor;
         d_sigma[ray * S + i] = t.active ? dalpha * t.delta_e : 0.f;

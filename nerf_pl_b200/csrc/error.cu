@@ -4,6 +4,7 @@
 
 namespace nrf {
 static thread_local char g_err[512] = "";
+unsigned long long g_launches = 0;
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -13,6 +14,7 @@ void set_error(const char* fmt, ...) {
 }  // namespace nrf
 
 extern "C" int nrf_abi_version(void) { return 1; }
+extern "C" uint64_t nrf_launch_count(void) { return nrf::g_launches; }
 extern "C" const char* nrf_last_error(void) { return nrf::g_err; }
 extern "C" int nrf_check_device(void) {
   int dev = 0;

@@ -10,22 +10,16 @@ import torch
 from . import _lib, ops
 from .ops import _dev, _p, _stream
 
-_pack_cache = {}
+TC_BACKWARD = False   # flipped on when the tcgen05 dgrad/wgrad kernels are built
 
 
-def _packed_weights(spec, params):
-    """bf16 operand copies of the parameters, re-packed when any parameter was modified."""
-    key = tuple(p.data_ptr() for p in params)
-    ver = tuple(p._version for p in params)
-    hit = _pack_cache.get(key)
-    if hit is not None and hit[0] == ver:
-        return hit[1]
+def pack_weights(spec, params, out=None):
+    """bf16 UMMA operand images of the parameters (nrf_mlp_tc_pack).  Callers that own the parameters
+    (NeRF.packed_weights) cache the result per parameter version; there is no global cache, because device
+    addresses are recycled between models."""
     nbytes = _lib.load().nrf_mlp_tc_packed_bytes()
-    buf = hit[1] if hit is not None else torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
+    buf = out if out is not None else torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
     _lib.call("nrf_mlp_tc_pack", byref(spec.params_struct(params)), _p(buf), _stream())
-    if len(_pack_cache) > 64:
-        _pack_cache.clear()
-    _pack_cache[key] = (ver, buf)
     return buf
 
 
@@ -38,7 +32,7 @@ def _use_tc(spec, precision):
     return True
 
 
-def forward_rays(spec, params, rays, z, sigma_only, need_grad, precision, xyz_freqs=10, dir_freqs=4):
+def forward_rays(spec, params, rays, z, sigma_only, need_grad, precision, xyz_freqs=10, dir_freqs=4, packed=None):
     """Returns (sigma (N,S), rgb (N,S,3) or None, saved) — `saved` feeds backward_rays."""
     lib = _lib.load()
     N, S = z.shape
@@ -48,12 +42,13 @@ def forward_rays(spec, params, rays, z, sigma_only, need_grad, precision, xyz_fr
     if N == 0:
         return sigma, rgb, None
     if _use_tc(spec, precision):
-        packed = _packed_weights(spec, params)
-        nb = lib.nrf_mlp_tc_stash_bytes(N * S, int(sigma_only)) if need_grad else 0
+        if packed is None:
+            packed = pack_weights(spec, params)
+        nb = lib.nrf_mlp_tc_stash_bytes(N * S, int(sigma_only)) if (need_grad and TC_BACKWARD) else 0
         stash = torch.empty(nb, dtype=torch.uint8, device=dev) if nb else None
         _lib.call("nrf_mlp_tc_fwd", _p(packed), _p(rays), _p(z), N, S, int(sigma_only), _p(sigma), _p(rgb),
                   _p(stash), nb, _stream())
-        return sigma, rgb, ("tc", packed, stash)
+        return sigma, rgb, (("tc", packed, stash) if (TC_BACKWARD or not need_grad) else ("tc_recompute",))
     ps = spec.params_struct(params)
     nb = lib.nrf_mlp_fp32_workspace_bytes(byref(ps), N * S, N, int(sigma_only), int(need_grad))
     ws = torch.empty(nb, dtype=torch.uint8, device=dev)
@@ -69,7 +64,19 @@ def backward_rays(spec, params, rays, z, sigma_only, saved, d_sigma, d_rgb, rgb)
     if N == 0:
         return grads
     gs = spec.grads_struct(grads)
-    if saved[0] == "tc":
+    if saved[0] == "tc_recompute":
+        # interim: parameter gradients of the bf16 forward are evaluated by the fp32 kernels at the same
+        # weights (forward re-run with activations kept); replaced by the tcgen05 dgrad/wgrad kernels
+        ps = spec.params_struct(params)
+        nb = lib.nrf_mlp_fp32_workspace_bytes(byref(ps), N * S, N, int(sigma_only), 1)
+        ws = torch.empty(nb, dtype=torch.uint8, device=z.device)
+        sig2 = torch.empty(N, S, device=z.device)
+        rgb2 = None if sigma_only else torch.empty(N, S, 3, device=z.device)
+        _lib.call("nrf_mlp_fp32_fwd_rays", byref(ps), _p(rays), _p(z), N, S, 10, 4, int(sigma_only), 1, _p(sig2),
+                  _p(rgb2), _p(ws), nb, _stream())
+        _lib.call("nrf_mlp_fp32_bwd", byref(ps), byref(gs), None, N * S, N, S, int(sigma_only), _p(d_sigma),
+                  _p(d_rgb), _p(rgb2), _p(ws), nb, _stream())
+    elif saved[0] == "tc":
         _, packed, stash = saved
         nb = lib.nrf_mlp_tc_bwd_workspace_bytes(N * S, int(sigma_only))
         ws = torch.empty(nb, dtype=torch.uint8, device=z.device)
@@ -94,7 +101,7 @@ class RenderPass(torch.autograd.Function):
     def forward(ctx, rays, z, noise, cfg, *params):
         need_grad = any(ctx.needs_input_grad[4:])
         sigma, rgb_s, saved = forward_rays(cfg.spec, params, rays, z, cfg.sigma_only, need_grad, cfg.precision,
-                                           cfg.xyz_freqs, cfg.dir_freqs)
+                                           cfg.xyz_freqs, cfg.dir_freqs, getattr(cfg, "packed", None))
         c = ops.composite(sigma, rgb_s, z, rays, noise, cfg.noise_std, cfg.white_back)
         ctx.cfg, ctx.saved, ctx.n_params = cfg, saved, len(params)
         if need_grad:

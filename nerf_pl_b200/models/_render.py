@@ -31,8 +31,10 @@ def _model_cfg(model, embeddings, sigma_only, white_back, noise_std):
         raise RuntimeError("the fused renderer supports logscale Embedding frequency bands only")
     if ex.out_channels != spec.in_xyz or (not sigma_only and ed.out_channels != spec.in_dir):
         raise RuntimeError("Embedding out_channels do not match the NeRF in_channels")
+    precision = ops.get_mlp_precision()
+    packed = model.packed_weights() if (precision == "bf16" and spec.tc_capable) else None
     return SimpleNamespace(spec=spec, sigma_only=bool(sigma_only), white_back=bool(white_back),
-                           noise_std=float(noise_std), precision=ops.get_mlp_precision(),
+                           noise_std=float(noise_std), precision=precision, packed=packed,
                            xyz_freqs=int(ex.N_freqs), dir_freqs=int(ed.N_freqs))
 
 

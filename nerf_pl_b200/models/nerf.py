@@ -62,6 +62,19 @@ class NeRF(nn.Module):
         named = dict(self.named_parameters())
         return [named[n] for n in self._spec.names]
 
+    def packed_weights(self):
+        """bf16 tensor-core operand images of the current parameters, re-packed when any parameter changed
+        (optimizer steps bump the tensors' version counters) or moved."""
+        params = self.ordered_parameters()
+        tag = tuple((p.data_ptr(), p._version) for p in params)
+        cache = self.__dict__.get("_nrf_pack")
+        if cache is None or cache[0] != tag or cache[1].device != params[0].device:
+            buf = cache[1] if cache is not None and cache[1].device == params[0].device else None
+            with torch.no_grad():
+                buf = _mlp.pack_weights(self._spec, [p.detach() for p in params], buf)
+            self.__dict__["_nrf_pack"] = cache = (tag, buf)
+        return cache[1]
+
     def forward(self, x, sigma_only=False):
         """x: (B, in_xyz[+in_dir]) encoded input -> (B,4) [rgb, sigma] or (B,1) sigma."""
         if not x.is_cuda:

@@ -144,3 +144,69 @@ def test_sample_pdf_flip_rate_end_to_end_fp32(dev):
     flips = (zf.cpu() != aux["z_fine"]).float().mean().item()
     print(f"end-to-end fine-sample flip rate: {flips:.2e}")
     assert flips < 2e-3
+
+
+def test_tc_forward_vs_fp32_kernels(dev):
+    """bf16 tcgen05 MLP against the fp32 kernels on the same rays: per-sample sigma / rgb."""
+    from nerf_pl_b200.mlp import forward_rays
+    from nerf_pl_b200.models.nerf import NeRF
+    p = O.init_mlp_params(generator=torch.Generator().manual_seed(0))
+    m = NeRF().to(dev)
+    m.load_state_dict(p)
+    params = [t.detach() for t in m.ordered_parameters()]
+    for N, S, near, far in ((300, 64, 2.0, 6.0), (37, 192, 1.0, 200.0), (1, 5, 2.0, 6.0)):
+        rays = O.blender_rays(N, seed=5, near=near, far=far).to(dev)
+        z = torch.sort(torch.rand(N, S, generator=torch.Generator().manual_seed(6)) * (far - near) + near, -1)[0].to(dev)
+        for sigma_only in (False, True):
+            s32, c32, _ = forward_rays(m.spec, params, rays, z, sigma_only, False, "fp32")
+            s16, c16, _ = forward_rays(m.spec, params, rays, z, sigma_only, False, "bf16")
+            torch.cuda.synchronize()
+            es = (s16 - s32).abs().max().item()
+            scale = s32.abs().max().item()
+            print(f"N={N} S={S} far={far} sigma_only={sigma_only}: max|dsigma|={es:.3e} (|sigma|max {scale:.3e})", end="")
+            assert es < 2e-2 * max(1.0, scale), "bf16 sigma"
+            if not sigma_only:
+                ec = (c16 - c32).abs().max().item()
+                print(f" max|drgb|={ec:.3e}", end="")
+                assert ec < 2e-2, "bf16 rgb"
+            print()
+
+
+@pytest.mark.parametrize("variant,near,far,test_time", [("rgb", 2.0, 6.0, False), ("rgb", 2.0, 6.0, True),
+                                                        ("depth", 2.0, 6.0, False)])
+def test_full_width_bf16_vs_oracle(dev, variant, near, far, test_time):
+    """End-to-end with the tensor-core MLP: 2e-3 absolute on rgb/opacity, 2e-3*far on depth (north_star),
+    fine depths injected so bin flips do not enter."""
+    params, models, ref, got, aux, *_ = _full_width_case(dev, "bf16", variant, 256, 64, 64, near, far, False, test_time, 41)
+    # The reference's last interval is 1e10 long (rendering.py:171): a ray's opacity jumps between ~0 and 1 with
+    # the SIGN of the last sample's sigma(+noise).  Rays whose last raw sigma is within the bf16 error of zero
+    # sit on that discontinuity and are excluded (reported); they are a handful with random-init weights.
+    margin = 2e-3
+    stable = ((aux["raw_coarse"][:, -1].abs() > margin) & (aux["raw_fine"][:, -1].abs() > margin)).detach().numpy()
+    print(f"rays away from the last-sample discontinuity: {stable.mean():.3f}")
+    assert stable.mean() > 0.5
+    for k in sorted(ref):
+        r = ref[k].detach().numpy()
+        g = got[k].detach().cpu().numpy()
+        ok = ~np.isnan(r) & (stable if r.ndim == 1 else stable[:, None])
+        err = np.abs(g[ok] - r[ok]).max()
+        print(f"{k}: max abs err {err:.3e} (range {np.abs(r[ok]).max():.2f})")
+        tol = 2e-3 * (far if k.startswith("depth") else 1.0) * (20.0 if k.startswith("disp") else 1.0)
+        assert err < tol, k
+    if not test_time and variant == "rgb":
+        g = torch.Generator().manual_seed(5)
+        loss_r = loss_g = 0
+        for k in sorted(ref):
+            pr = torch.rand(ref[k].shape, generator=g)
+            loss_r = loss_r + (ref[k] * pr).sum()
+            loss_g = loss_g + (got[k] * pr.to(got[k].device)).sum()
+        loss_r.backward()
+        loss_g.backward()
+        worst = 0.0
+        for mi, m in enumerate(models):
+            for pn, pv in m.named_parameters():
+                r = params[mi][pn].grad.numpy()
+                rel = np.linalg.norm(pv.grad.cpu().numpy() - r) / (np.linalg.norm(r) + 1e-12)
+                worst = max(worst, rel)
+                assert rel < 5e-2, f"grad {mi}/{pn}: relative L2 error {rel:.2e}"   # bf16 mode: stated 5e-2
+        print(f"bf16 parameter gradients: worst relative L2 error {worst:.2e}")
