@@ -398,11 +398,3 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
   return sigma_only ? launch_fwd<false, false>(a, st) : launch_fwd<true, false>(a, st);
 }
 
-// ---- backward: placeholder until the dgrad/wgrad kernels land --------------------------------------
-extern "C" size_t nrf_mlp_tc_bwd_workspace_bytes(int64_t, int) { return 0; }
-extern "C" int nrf_mlp_tc_bwd(const void*, const nrf_mlp_grads*, const float*, const float*, int64_t, int, int,
-                              const float*, const float*, const float*, const void*, size_t, void*, size_t,
-                              nrf_stream_t) {
-  set_error("nrf_mlp_tc_bwd: not built yet");
-  return NRF_ERR_UNSUPPORTED;
-}

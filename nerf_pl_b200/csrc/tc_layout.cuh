@@ -66,6 +66,11 @@ constexpr int kStashChunksSigma = kStashFeat;     // 34 (no feat / dmid; dir slo
 constexpr int kMaskWordsFull = 8 * 128 * 8 + 128 * 4;
 constexpr int kMaskWordsSigma = 8 * 128 * 8;
 
+// ---- per-tile G stash written by the dgrad kernel (dL/d pre-activation images) ---------------------
+// G0..G7 at chunk 4*l, G8 (xyz_final) at 32..35, G9 (dir layer, 128 wide) at 36..37
+constexpr int kGstashG8 = 32, kGstashG9 = 36;
+__host__ __device__ inline size_t gstash_tile_bytes(bool full) { return (size_t)(full ? 38 : 32) * kActChunkBytes; }
+
 __host__ __device__ inline size_t stash_tile_bytes(bool full) {
   return (size_t)(full ? kStashChunksFull : kStashChunksSigma) * kActChunkBytes;
 }

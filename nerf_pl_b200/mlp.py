@@ -10,7 +10,7 @@ import torch
 from . import _lib, ops
 from .ops import _dev, _p, _stream
 
-TC_BACKWARD = False   # flipped on when the tcgen05 dgrad/wgrad kernels are built
+TC_BACKWARD = True    # False: parameter gradients of the bf16 forward via the fp32 kernels (debug aid)
 
 
 def pack_weights(spec, params, out=None):
