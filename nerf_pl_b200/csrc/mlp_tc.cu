@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "embed.cuh"
 #include "tc_common.cuh"
+#include "tc_epilogue.cuh"
 #include "tc_layout.cuh"
 
 namespace nrf {
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
         if (et == 0) bulk_wait_read0();
         named_bar_sync(1, kEpiThreads);
       }
-      // ---- encode this tile's points: thread (er, part) fills half of row er ----
+      // ---- encode this tile's points: thread (er, part) fills 32 columns of row er ----
       {
         const int er = et & 127, part = et >> 7;
         int64_t gr = (int64_t)tile * kTileM + er;
@@ -171,38 +172,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
         float p[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) p[c] = sample_point(a.rays, ray, zv, c);
-        if (part == 0) {
-#pragma unroll
-          for (int c = 0; c < 3; ++c) st_bf16(s_enc, er, c, p[c]);
-        }
-        for (int k = part * 5; k < part * 5 + 5; ++k) {
-          const float f = exp2f((float)k);
-#pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            float sn, cs;
-            sincosf(__fmul_rn(f, p[c]), &sn, &cs);
-            st_bf16(s_enc, er, 3 + (2 * k) * 3 + c, sn);
-            st_bf16(s_enc, er, 3 + (2 * k + 1) * 3 + c, cs);
-          }
-        }
+        encode_store<10>(part, p, smem_u32(s_enc), er);
         if (kFull) {
           float d[3];
 #pragma unroll
           for (int c = 0; c < 3; ++c) d[c] = __ldg(a.rays + ray * 8 + 3 + c);
-          if (part == 0) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) st_bf16(s_dir, er, c, d[c]);
-          }
-          for (int k = part * 2; k < part * 2 + 2; ++k) {
-            const float f = exp2f((float)k);
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-              float sn, cs;
-              sincosf(__fmul_rn(f, d[c]), &sn, &cs);
-              st_bf16(s_dir, er, 3 + (2 * k) * 3 + c, sn);
-              st_bf16(s_dir, er, 3 + (2 * k + 1) * 3 + c, cs);
-            }
-          }
+          if (part == 0) encode_store<4>(0, d, smem_u32(s_dir), er);
         }
       }
       fence_async_smem();
@@ -226,35 +201,16 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
           named_bar_sync(1, kEpiThreads);
         }
         if (L < 9) {
-          const float* bias = s_aux + (L < 8 ? AuxOffsets::bias + L * 256 : AuxOffsets::bias_final);
           const bool relu = L < 8;
+          const uint32_t bias_s = smem_u32(s_aux + (L < 8 ? AuxOffsets::bias + L * 256 : AuxOffsets::bias_final));
+          const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma);
+          const uint32_t act_s = smem_u32(s_act);
+          const RowSwz rsw(row);
           float sig_part = 0.f;
           uint32_t mw[4];
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const int c0 = h * 128 + g * 32;
-            uint32_t v[32];
-            tmem_ld32(t_row + c0, v);
-            tmem_ld_wait();
-            uint32_t m = 0, pk[16];
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              float f0 = __uint_as_float(v[j]) + bias[c0 + j];
-              float f1 = __uint_as_float(v[j + 1]) + bias[c0 + j + 1];
-              if (relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
-              m |= (f0 > 0.f ? 1u : 0u) << j;
-              m |= (f1 > 0.f ? 1u : 0u) << (j + 1);
-              if (L == 7) sig_part += f0 * s_aux[AuxOffsets::w_sigma + c0 + j] + f1 * s_aux[AuxOffsets::w_sigma + c0 + j + 1];
-              pk[j >> 1] = pack_bf16(f0, f1);
-            }
-            mw[g] = m;
-            uint8_t* chunk = s_act + (c0 >> 6) * kActChunkBytes;
-            const int p0 = (c0 & 63) >> 3;
-#pragma unroll
-            for (int p = 0; p < 4; ++p)
-              *reinterpret_cast<uint4*>(chunk + sw128_off(row, p0 + p)) =
-                  make_uint4(pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
-          }
+          if (L == 7) epi_hidden128<true, kTrain, true>(t_row, h * 128, rsw, act_s, bias_s, wsig_s, mw, sig_part);
+          else if (relu) epi_hidden128<true, kTrain, false>(t_row, h * 128, rsw, act_s, bias_s, wsig_s, mw, sig_part);
+          else epi_hidden128<false, false, false>(t_row, h * 128, rsw, act_s, bias_s, wsig_s, mw, sig_part);
           if (kTrain && relu)
             *reinterpret_cast<uint4*>(mask_tile + ((size_t)L * 128 + row) * 8 + h * 4) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
           if (L == 7) {
@@ -279,33 +235,36 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const FwdArgs a) {
           // direction layer: N = 128; rgb head on the fp32 accumulators (nerf.py:119-121)
           float r0 = 0.f, r1 = 0.f, r2 = 0.f;
           uint32_t mw[2];
+          const uint32_t bdir_s = smem_u32(s_aux + AuxOffsets::bias_dir), wrgb_s = smem_u32(s_aux + AuxOffsets::w_rgb);
+          const RowSwz rsw(row);
 #pragma unroll
           for (int g = 0; g < 2; ++g) {
             const int c0 = h * 64 + g * 32;
             uint32_t v[32];
             tmem_ld32(t_row + c0, v);
-            tmem_ld_wait();
+            tmem_ld_wait_dep(v);
             uint32_t m = 0, pk[16];
 #pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              const float f0 = fmaxf(__uint_as_float(v[j]) + s_aux[AuxOffsets::bias_dir + c0 + j], 0.f);
-              const float f1 = fmaxf(__uint_as_float(v[j + 1]) + s_aux[AuxOffsets::bias_dir + c0 + j + 1], 0.f);
-              m |= (f0 > 0.f ? 1u : 0u) << j;
-              m |= (f1 > 0.f ? 1u : 0u) << (j + 1);
-              const float* wr = s_aux + AuxOffsets::w_rgb + c0 + j;
-              r0 += f0 * wr[0] + f1 * wr[1];
-              r1 += f0 * wr[128] + f1 * wr[129];
-              r2 += f0 * wr[256] + f1 * wr[257];
-              pk[j >> 1] = pack_bf16(f0, f1);
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b = ld_shared_f4(bdir_s + (c0 + j) * 4);
+              const float x0 = __uint_as_float(v[j]) + b.x, x1 = __uint_as_float(v[j + 1]) + b.y;
+              const float x2 = __uint_as_float(v[j + 2]) + b.z, x3 = __uint_as_float(v[j + 3]) + b.w;
+              if (kTrain) { m = push_sign(m, x0); m = push_sign(m, x1); m = push_sign(m, x2); m = push_sign(m, x3); }
+              const float f0 = fmaxf(x0, 0.f), f1 = fmaxf(x1, 0.f), f2 = fmaxf(x2, 0.f), f3 = fmaxf(x3, 0.f);
+              const float4 w0 = ld_shared_f4(wrgb_s + (c0 + j) * 4), w1 = ld_shared_f4(wrgb_s + (128 + c0 + j) * 4),
+                           w2 = ld_shared_f4(wrgb_s + (256 + c0 + j) * 4);
+              r0 += f0 * w0.x + f1 * w0.y + f2 * w0.z + f3 * w0.w;
+              r1 += f0 * w1.x + f1 * w1.y + f2 * w1.z + f3 * w1.w;
+              r2 += f0 * w2.x + f1 * w2.y + f2 * w2.z + f3 * w2.w;
+              pk[j >> 1] = cvt_bf16x2(f0, f1);
+              pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
             }
-            mw[g] = m;
+            mw[g] = ~m;
             if (kTrain) {
-              uint8_t* chunk = s_act + h * kActChunkBytes;  // 64 columns per half = one chunk
-              const int p0 = (g * 32) >> 3;
+              const uint32_t chunk = smem_u32(s_act) + (uint32_t)h * kActChunkBytes;  // 64 columns per half = one chunk
 #pragma unroll
               for (int p = 0; p < 4; ++p)
-                *reinterpret_cast<uint4*>(chunk + sw128_off(row, p0 + p)) =
-                    make_uint4(pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+                st_shared_v4(chunk + rsw.piece(g * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
             }
           }
           if (kTrain) *reinterpret_cast<uint2*>(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + h * 2) = make_uint2(mw[0], mw[1]);

@@ -14,6 +14,7 @@
 // (mlp_tc_wgrad.cu) consumes those images as MN-major UMMA operands.
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "tc_epilogue.cuh"
 #include "tc_layout.cuh"
 
 namespace nrf {
@@ -143,45 +144,55 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArg
         }
         if (h == 0) *reinterpret_cast<float4*>(a.dpre + ((size_t)tile * kTileM + row) * 4) = make_float4(dp[0], dp[1], dp[2], 0.f);
         const uint2 mw = *reinterpret_cast<const uint2*>(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + h * 2);
-        uint8_t* chunk = s_act + h * kActChunkBytes;
+        const uint32_t chunk = smem_u32(s_act) + (uint32_t)h * kActChunkBytes;
+        const uint32_t wrgb_s = smem_u32(s_aux + AuxOffsets::w_rgb);
+        const RowSwz rsw(row);
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
           const uint32_t m = g ? mw.y : mw.x;
           uint32_t pk[16];
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            const float* wr = s_aux + AuxOffsets::w_rgb + h * 64 + g * 32 + j;
-            float f0 = dp[0] * wr[0] + dp[1] * wr[128] + dp[2] * wr[256];
-            float f1 = dp[0] * wr[1] + dp[1] * wr[129] + dp[2] * wr[257];
-            if (!((m >> j) & 1u)) f0 = 0.f;
-            if (!((m >> (j + 1)) & 1u)) f1 = 0.f;
-            pk[j >> 1] = pack_bf16(f0, f1);
+          for (int j = 0; j < 32; j += 4) {
+            const int c = h * 64 + g * 32 + j;
+            const float4 w0 = ld_shared_f4(wrgb_s + c * 4), w1 = ld_shared_f4(wrgb_s + (128 + c) * 4),
+                         w2 = ld_shared_f4(wrgb_s + (256 + c) * 4);
+            float f0 = dp[0] * w0.x + dp[1] * w1.x + dp[2] * w2.x;
+            float f1 = dp[0] * w0.y + dp[1] * w1.y + dp[2] * w2.y;
+            float f2 = dp[0] * w0.z + dp[1] * w1.z + dp[2] * w2.z;
+            float f3 = dp[0] * w0.w + dp[1] * w1.w + dp[2] * w2.w;
+            f0 = mask_bit(m, j) ? f0 : 0.f;
+            f1 = mask_bit(m, j + 1) ? f1 : 0.f;
+            f2 = mask_bit(m, j + 2) ? f2 : 0.f;
+            f3 = mask_bit(m, j + 3) ? f3 : 0.f;
+            pk[j >> 1] = cvt_bf16x2(f0, f1);
+            pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
 #pragma unroll
           for (int p = 0; p < 4; ++p)
-            *reinterpret_cast<uint4*>(chunk + sw128_off(row, g * 4 + p)) =
-                make_uint4(pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+            st_shared_v4(chunk + rsw.piece(g * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
         }
       } else {
         const uint4 mw4 = *reinterpret_cast<const uint4*>(mask_tile + ((size_t)7 * 128 + row) * 8 + h * 4);
         const uint32_t mw[4] = {mw4.x, mw4.y, mw4.z, mw4.w};
+        const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma), act_s = smem_u32(s_act);
+        const RowSwz rsw(row);
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           const int c0 = h * 128 + g * 32;
           uint32_t pk[16];
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            float f0 = dsig * s_aux[AuxOffsets::w_sigma + c0 + j], f1 = dsig * s_aux[AuxOffsets::w_sigma + c0 + j + 1];
-            if (!((mw[g] >> j) & 1u)) f0 = 0.f;
-            if (!((mw[g] >> (j + 1)) & 1u)) f1 = 0.f;
-            pk[j >> 1] = pack_bf16(f0, f1);
+          for (int j = 0; j < 32; j += 4) {
+            const float4 w = ld_shared_f4(wsig_s + (c0 + j) * 4);
+            const float f0 = mask_bit(mw[g], j) ? dsig * w.x : 0.f, f1 = mask_bit(mw[g], j + 1) ? dsig * w.y : 0.f;
+            const float f2 = mask_bit(mw[g], j + 2) ? dsig * w.z : 0.f, f3 = mask_bit(mw[g], j + 3) ? dsig * w.w : 0.f;
+            pk[j >> 1] = cvt_bf16x2(f0, f1);
+            pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
-          uint8_t* chunk = s_act + (c0 >> 6) * kActChunkBytes;
+          const uint32_t chunk = act_s + (uint32_t)(c0 >> 6) * kActChunkBytes;
           const int p0 = (c0 & 63) >> 3;
 #pragma unroll
           for (int p = 0; p < 4; ++p)
-            *reinterpret_cast<uint4*>(chunk + sw128_off(row, p0 + p)) =
-                make_uint4(pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+            st_shared_v4(chunk + rsw.piece(p0 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
         }
       }
       fence_async_smem();
@@ -207,30 +218,11 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArg
           const uint4 m4 = *reinterpret_cast<const uint4*>(mask_tile + ((size_t)t * 128 + row) * 8 + h * 4);
           mw[0] = m4.x; mw[1] = m4.y; mw[2] = m4.z; mw[3] = m4.w;
         }
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int c0 = h * 128 + g * 32;
-          uint32_t v[32];
-          tmem_ld32(t_row + c0, v);
-          tmem_ld_wait();
-          uint32_t pk[16];
-#pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            float f0 = __uint_as_float(v[j]), f1 = __uint_as_float(v[j + 1]);
-            if (kFull && t == 7) {
-              f0 += dsig * s_aux[AuxOffsets::w_sigma + c0 + j];
-              f1 += dsig * s_aux[AuxOffsets::w_sigma + c0 + j + 1];
-            }
-            if (!((mw[g] >> j) & 1u)) f0 = 0.f;
-            if (!((mw[g] >> (j + 1)) & 1u)) f1 = 0.f;
-            pk[j >> 1] = pack_bf16(f0, f1);
-          }
-          uint8_t* chunk = s_act + (c0 >> 6) * kActChunkBytes;
-          const int p0 = (c0 & 63) >> 3;
-#pragma unroll
-          for (int p = 0; p < 4; ++p)
-            *reinterpret_cast<uint4*>(chunk + sw128_off(row, p0 + p)) =
-                make_uint4(pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+        {
+          const RowSwz rsw(row);
+          const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma), act_s = smem_u32(s_act);
+          if (kFull && t == 7) epi_dgrad128<true>(t_row, h * 128, rsw, act_s, mw, dsig, wsig_s);
+          else epi_dgrad128<false>(t_row, h * 128, rsw, act_s, mw, dsig, wsig_s);
         }
         fence_async_smem();
         named_bar_sync(1, kDgEpiThreads);
