@@ -172,6 +172,13 @@ int nrf_shadow_bwd(const float* cam_pixels, const float* cam_depth, const float*
 int nrf_normed_w(const float* pixel_depth, const float* value, const float* passthrough, const float* M,
                  int64_t n, float* out, nrf_stream_t stream);
 
+/* Diagnostics (not on the product path): lane-parallel cp.async.bulk streaming benchmark used to choose
+ * the stash layout and the weight-ring geometry (tools/stream_bench.py).  Moves
+ * grid * steps * n_streams * piece bytes from `base` (+ strides) into shared memory. */
+int nrf_dbg_stream(const void* base, unsigned long long cta_stride, unsigned long long stream_stride,
+                   unsigned long long tile_stride, uint32_t piece, int n_streams, int ppc, int wrap_tiles,
+                   int steps, int stages, int grid, nrf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

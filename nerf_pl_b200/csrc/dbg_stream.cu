@@ -1,0 +1,77 @@
+// Measurement aid (not on the product path): how fast can persistent CTAs pull data into shared memory
+// with lane-parallel cp.async.bulk copies, as a function of piece size and address pattern?  Used to
+// choose the stash layout (HBM streams of the wgrad kernel) and the weight-ring geometry (L2 streams of
+// the forward / dgrad kernels).  DESIGN.md §4 quotes the numbers; tools/stream_bench.py drives it.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace nrf {
+namespace tc {
+
+struct StreamArgs {
+  const uint8_t* base;
+  unsigned long long cta_stride, stream_stride, tile_stride;
+  uint32_t piece;      // bytes per copy (multiple of 16)
+  int n_streams;       // copies per stage (<= 32)
+  int ppc;             // pieces per chunk: consecutive steps walk `ppc` adjacent pieces, then jump by tile_stride
+  int wrap_tiles;      // tiles wrap around after this many (0 = never): L2-resident working sets
+  int steps, stages;
+};
+
+__global__ void __launch_bounds__(64, 1) stream_kernel(const __grid_constant__ StreamArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t stage_bytes = a.piece * a.n_streams;
+  uint64_t* bar_full = reinterpret_cast<uint64_t*>(smem + (size_t)a.stages * stage_bytes);
+  uint64_t* bar_empty = bar_full + a.stages;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const uint8_t* src = a.base + (size_t)blockIdx.x * a.cta_stride + (size_t)lane * a.stream_stride;
+    int stage = 0, ph = 0, tile = 0, sub = 0;
+    for (int s = 0; s < a.steps; ++s) {
+      if (lane == 0) {
+        mbar_wait(bar_empty + stage, ph ^ 1);
+        mbar_arrive_expect_tx(bar_full + stage, stage_bytes);
+      }
+      __syncwarp();
+      if (lane < a.n_streams)
+        bulk_g2s(smem + (size_t)stage * stage_bytes + lane * a.piece,
+                 src + (size_t)tile * a.tile_stride + (size_t)sub * a.piece, a.piece, bar_full + stage);
+      if (++stage == a.stages) { stage = 0; ph ^= 1; }
+      if (++sub == a.ppc) { sub = 0; if (++tile == a.wrap_tiles) tile = 0; }
+    }
+  } else if (lane == 0) {
+    int stage = 0, ph = 0;
+    for (int s = 0; s < a.steps; ++s) {
+      mbar_wait(bar_full + stage, ph);
+      mbar_arrive(bar_empty + stage);
+      if (++stage == a.stages) { stage = 0; ph ^= 1; }
+    }
+  }
+}
+
+}  // namespace tc
+}  // namespace nrf
+
+using namespace nrf;
+using namespace nrf::tc;
+
+// Launches `grid` CTAs; returns NRF_OK.  Total bytes moved = grid * steps * n_streams * piece.
+extern "C" int nrf_dbg_stream(const void* base, unsigned long long cta_stride, unsigned long long stream_stride,
+                              unsigned long long tile_stride, uint32_t piece, int n_streams, int ppc, int wrap_tiles,
+                              int steps, int stages, int grid, nrf_stream_t stream) {
+  NRF_REQUIRE(base && piece % 16 == 0 && n_streams >= 1 && n_streams <= 32 && stages >= 1 && ppc >= 1, "nrf_dbg_stream: bad args");
+  const size_t smem_bytes = (size_t)stages * piece * n_streams + 16 * stages + 1024;
+  NRF_REQUIRE(smem_bytes <= 227 * 1024, "nrf_dbg_stream: ring too large");
+  NRF_CUDA(cudaFuncSetAttribute(stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  StreamArgs a{static_cast<const uint8_t*>(base), cta_stride, stream_stride, tile_stride, piece, n_streams, ppc,
+               wrap_tiles, steps, stages};
+  stream_kernel<<<grid, 64, smem_bytes, as_stream(stream)>>>(a);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
