@@ -6,9 +6,10 @@
 //   G7 = (G8 . W_final + d_sigma w_sigma) (x) relu'(h7)             UMMA  M128 N256 K256 + rank-1 on CUDA cores
 //   G_{l-1} = (G_l . W_l[:, h part]) (x) relu'(h_{l-1}),  l = 7..1  UMMA  M128 N256 K256
 //
-// Same warp-specialised structure as the forward kernel (mlp_tc.cu): bulk-copy weight ring
-// (transposed, pre-packed images), one UMMA issuer thread, eight epilogue warps that turn the
-// TMEM accumulator into the next A operand (bf16, SWIZZLE_128B) in shared memory.  ReLU
+// Same warp-specialised, chunk-pipelined structure as the forward kernel (mlp_tc.cu): bulk-copy weight
+// ring (transposed, pre-packed images), one UMMA issuer thread, two alternating TMEM accumulators,
+// eight epilogue warps that turn the accumulator into the next A operand (bf16, SWIZZLE_128B) in shared
+// memory 64 columns at a time while the next layer's MMAs already consume the finished chunks.  ReLU
 // derivatives come from the 1-bit sign masks the forward kernel stashed (32 B per row and layer).
 // Every G_l image is also streamed to HBM with a bulk store; the wgrad kernel
 // (mlp_tc_wgrad.cu) consumes those images as MN-major UMMA operands.
@@ -21,13 +22,15 @@ namespace nrf {
 namespace tc {
 
 constexpr int kDgStages = 3;
-constexpr int kDgEpiThreads = 256;
+constexpr int kDgEpiWarps = 8;
+constexpr int kDgEpiThreads = kDgEpiWarps * 32;
 constexpr int kDgThreads = 64 + kDgEpiThreads;
 constexpr uint32_t kDgSmAct = 0;
-constexpr uint32_t kDgSmRing = kDgSmAct + 4 * kActChunkBytes;
+constexpr uint32_t kDgSmPro = kDgSmAct + 4 * kActChunkBytes;      // full mode: staging of the next tile's G9 (2 chunks)
+constexpr uint32_t kDgSmRing = kDgSmPro + 2 * kActChunkBytes;
 constexpr uint32_t kDgSmAux = kDgSmRing + kDgStages * kChunkBytes256;
 constexpr uint32_t kDgSmBars = kDgSmAux + AuxOffsets::count * 4;
-constexpr uint32_t kDgSmTotal = kDgSmBars + 128;
+constexpr uint32_t kDgSmTotal = kDgSmBars + 256;
 
 struct DgradArgs {
   const uint8_t* packed;
@@ -41,19 +44,22 @@ struct DgradArgs {
   float* dpre;             // (tiles*128, 4): d_rgb * rgb (1-rgb), written for the wgrad kernel (full mode)
 };
 
+constexpr int kDgBarPro = 4, kDgNumBarA = 5;   // A-operand readiness: act chunks 0..3, G9 staging
+
 template <bool kFull>
-__global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArgs a) {
+__global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_constant__ DgradArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* s_act = smem + kDgSmAct;
+  uint8_t* s_pro = smem + kDgSmPro;
   uint8_t* s_ring = smem + kDgSmRing;
   float* s_aux = reinterpret_cast<float*>(smem + kDgSmAux);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kDgSmBars);
   uint64_t* bar_full = bars;
   uint64_t* bar_empty = bars + kDgStages;
-  uint64_t* bar_act = bars + 2 * kDgStages;
-  uint64_t* bar_acc = bars + 2 * kDgStages + 1;
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 2 * kDgStages + 2);
+  uint64_t* bar_a = bars + 2 * kDgStages;     // [kDgNumBarA]
+  uint64_t* bar_acc = bar_a + kDgNumBarA;     // [2]
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_acc + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kMmaLayers = kFull ? 9 : 7;
@@ -62,11 +68,12 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArg
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kDgStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
-    mbar_init(bar_act, kDgEpiThreads);
+    for (int s = 0; s < kDgNumBarA; ++s) mbar_init(bar_a + s, kDgEpiWarps);
     mbar_init(bar_acc, 1);
+    mbar_init(bar_acc + 1, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(s_tmem, 256);
+  if (warp == 1) tmem_alloc(s_tmem, 512);
   if (warp >= 2) {
     const float* gaux = reinterpret_cast<const float*>(a.packed + kPackedAuxOff);
     for (int i = threadIdx.x - 64; i < AuxOffsets::count; i += kDgEpiThreads) s_aux[i] = gaux[i];
@@ -78,61 +85,73 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArg
 
   if (warp == 0) {
     if (lane == 0) {
-      uint32_t it = 0;
+      uint32_t stage = 0, ph = 0;
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        for (int ci = 0; ci < kChunks; ++ci, ++it) {
-          const uint32_t stage = it % kDgStages, ph = (it / kDgStages) & 1;
+        for (int ci = 0; ci < kChunks; ++ci) {
           mbar_wait(bar_empty + stage, ph ^ 1);
           mbar_arrive_expect_tx(bar_full + stage, kChunkBytes256);
           bulk_g2s(s_ring + stage * kChunkBytes256,
                    a.packed + kPackedBwdOff + (size_t)(kFirstChunk + ci) * kChunkBytes256, kChunkBytes256,
                    bar_full + stage);
+          if (++stage == kDgStages) { stage = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      uint32_t it = 0, act_it = 0;
+      uint32_t stage = 0, ph = 0, a_par = 0, g = 0;   // g: running layer counter (accumulators alternate across tiles too)
       const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        for (int i = 0; i < kMmaLayers; ++i) {
-          mbar_wait(bar_act, act_it & 1);
-          ++act_it;
-          tc_fence_after();
-          const int nchunks = (kFull && i == 0) ? 2 : 4;
-          for (int c = 0; c < nchunks; ++c, ++it) {
-            const uint32_t stage = it % kDgStages, ph = (it / kDgStages) & 1;
+#pragma unroll 1
+        for (int i = 0; i < kMmaLayers; ++i, ++g) {
+          const bool from_pro = kFull && i == 0;
+          const int nchunks = from_pro ? 2 : 4;
+          const uint32_t d_tmem = tmem_base + (g & 1u) * 256;
+          for (int c = 0; c < nchunks; ++c) {
+            const int src = from_pro ? kDgBarPro : c;
+            if (!from_pro || c == 0) {
+              mbar_wait(bar_a + src, (a_par >> src) & 1u);
+              a_par ^= 1u << src;
+            }
             mbar_wait(bar_full + stage, ph);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(s_act + c * kActChunkBytes), b_addr = smem_u32(s_ring + stage * kChunkBytes256);
+            const uint32_t a_addr = smem_u32((from_pro ? s_pro : s_act) + c * kActChunkBytes);
+            const uint32_t b_addr = smem_u32(s_ring + stage * kChunkBytes256);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              umma_ss(tmem_base, make_desc_sw128(a_addr + k * 32, 16, 1024), make_desc_sw128(b_addr + k * 32, 16, 1024),
+              umma_ss(d_tmem, make_desc_sw128(a_addr + k * 32, 16, 1024), make_desc_sw128(b_addr + k * 32, 16, 1024),
                       idesc, (c | k) != 0);
             umma_commit(bar_empty + stage);
+            if (++stage == kDgStages) { stage = 0; ph ^= 1; }
           }
-          umma_commit(bar_acc);
+          umma_commit(bar_acc + (g & 1u));
         }
       }
     }
   } else {
     const int et = threadIdx.x - 64;
-    const int q = warp & 3, h = (warp - 2) >> 2;
+    const int q = warp & 3, sub = (warp - 2) >> 2;   // TMEM lane quarter; 32-column half of every 64-column chunk
     const int row = q * 32 + lane;
-    const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16);
-    uint32_t acc_it = 0;
-    bool store_pending = false;
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+    const RowSwz rsw(row);
+    const uint32_t act_s = smem_u32(s_act), pro_s = smem_u32(s_pro);
+    const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma), wrgb_s = smem_u32(s_aux + AuxOffsets::w_rgb);
+    uint32_t g = 0;   // running layer counter, mirrors the UMMA issuer
+
+    auto signal = [&](int idx) {
+      fence_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_a + idx);
+    };
+    // first A operand of a tile's chain, on CUDA cores.  Returns d_sigma of this thread's row.
+    //   full mode : G9 -> s_pro (2 chunks), also writes dpre and the G9 image
+    //   sigma-only: G7 = d_sigma * w_sigma (x) relu'(h7) -> s_act (4 chunks), also writes the G7 image
+    auto prologue = [&](int tile) -> float {
       uint8_t* g_tile = a.gstash + (size_t)tile * gstash_tile_bytes(kFull);
       const uint32_t* mask_tile = a.masks + (size_t)tile * mask_tile_words(kFull);
       const int64_t grow = (int64_t)tile * kTileM + row;
       const bool valid = grow < a.n_rows;
       const float dsig = valid ? __ldg(a.d_sigma + grow) : 0.f;
-      // ---- prologue: the first A operand of the chain, on CUDA cores ----
-      if (store_pending) {  // the previous tile's last image store still reads s_act
-        if (et == 0) bulk_wait_read0();
-        named_bar_sync(1, kDgEpiThreads);
-      }
       if (kFull) {
         float dp[3] = {0.f, 0.f, 0.f};
         if (valid) {
@@ -142,20 +161,17 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArg
             dp[c] = __ldg(a.d_rgb + grow * 3 + c) * y * (1.0f - y);  // sigmoid' (nerf.py:79-81)
           }
         }
-        if (h == 0) *reinterpret_cast<float4*>(a.dpre + ((size_t)tile * kTileM + row) * 4) = make_float4(dp[0], dp[1], dp[2], 0.f);
-        const uint2 mw = *reinterpret_cast<const uint2*>(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + h * 2);
-        const uint32_t chunk = smem_u32(s_act) + (uint32_t)h * kActChunkBytes;
-        const uint32_t wrgb_s = smem_u32(s_aux + AuxOffsets::w_rgb);
-        const RowSwz rsw(row);
+        if (sub == 0) *reinterpret_cast<float4*>(a.dpre + ((size_t)tile * kTileM + row) * 4) = make_float4(dp[0], dp[1], dp[2], 0.f);
+        const uint2 mw = *reinterpret_cast<const uint2*>(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + sub * 2);
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
-          const uint32_t m = g ? mw.y : mw.x;
+        for (int c = 0; c < 2; ++c) {
+          const uint32_t m = c ? mw.y : mw.x;
           uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            const int c = h * 64 + g * 32 + j;
-            const float4 w0 = ld_shared_f4(wrgb_s + c * 4), w1 = ld_shared_f4(wrgb_s + (128 + c) * 4),
-                         w2 = ld_shared_f4(wrgb_s + (256 + c) * 4);
+            const int col = c * 64 + sub * 32 + j;
+            const float4 w0 = ld_shared_f4(wrgb_s + col * 4), w1 = ld_shared_f4(wrgb_s + (128 + col) * 4),
+                         w2 = ld_shared_f4(wrgb_s + (256 + col) * 4);
             float f0 = dp[0] * w0.x + dp[1] * w1.x + dp[2] * w2.x;
             float f1 = dp[0] * w0.y + dp[1] * w1.y + dp[2] * w2.y;
             float f2 = dp[0] * w0.z + dp[1] * w1.z + dp[2] * w2.z;
@@ -167,74 +183,99 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArg
             pk[j >> 1] = cvt_bf16x2(f0, f1);
             pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
+          const uint32_t chunk_s = pro_s + (uint32_t)c * kActChunkBytes;
 #pragma unroll
           for (int p = 0; p < 4; ++p)
-            st_shared_v4(chunk + rsw.piece(g * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+            st_shared_v4(chunk_s + rsw.piece(sub * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+        }
+        signal(kDgBarPro);
+        named_bar_sync(1, kDgEpiThreads);
+        if (et == 0) {
+          bulk_s2g(g_tile + (size_t)kGstashG9 * kActChunkBytes, s_pro, 2 * kActChunkBytes);
+          bulk_commit();
         }
       } else {
-        const uint4 mw4 = *reinterpret_cast<const uint4*>(mask_tile + ((size_t)7 * 128 + row) * 8 + h * 4);
+        const uint4 mw4 = *reinterpret_cast<const uint4*>(mask_tile + ((size_t)7 * 128 + row) * 8 + sub * 4);
         const uint32_t mw[4] = {mw4.x, mw4.y, mw4.z, mw4.w};
-        const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma), act_s = smem_u32(s_act);
-        const RowSwz rsw(row);
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int c0 = h * 128 + g * 32;
+        for (int c = 0; c < 4; ++c) {
           uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            const float4 w = ld_shared_f4(wsig_s + (c0 + j) * 4);
-            const float f0 = mask_bit(mw[g], j) ? dsig * w.x : 0.f, f1 = mask_bit(mw[g], j + 1) ? dsig * w.y : 0.f;
-            const float f2 = mask_bit(mw[g], j + 2) ? dsig * w.z : 0.f, f3 = mask_bit(mw[g], j + 3) ? dsig * w.w : 0.f;
+            const float4 w = ld_shared_f4(wsig_s + (c * 64 + sub * 32 + j) * 4);
+            const float f0 = mask_bit(mw[c], j) ? dsig * w.x : 0.f, f1 = mask_bit(mw[c], j + 1) ? dsig * w.y : 0.f;
+            const float f2 = mask_bit(mw[c], j + 2) ? dsig * w.z : 0.f, f3 = mask_bit(mw[c], j + 3) ? dsig * w.w : 0.f;
             pk[j >> 1] = cvt_bf16x2(f0, f1);
             pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
-          const uint32_t chunk = act_s + (uint32_t)(c0 >> 6) * kActChunkBytes;
-          const int p0 = (c0 & 63) >> 3;
+          const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
 #pragma unroll
           for (int p = 0; p < 4; ++p)
-            st_shared_v4(chunk + rsw.piece(p0 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+            st_shared_v4(chunk_s + rsw.piece(sub * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+          signal(c);
+        }
+        named_bar_sync(1, kDgEpiThreads);
+        if (et == 0) {
+          bulk_s2g(g_tile + (size_t)(4 * 7) * kActChunkBytes, s_act, 4 * kActChunkBytes);
+          bulk_commit();
         }
       }
-      fence_async_smem();
-      named_bar_sync(1, kDgEpiThreads);
-      if (et == 0) {
-        if (kFull) bulk_s2g(g_tile + (size_t)kGstashG9 * kActChunkBytes, s_act, 2 * kActChunkBytes);
-        else bulk_s2g(g_tile + (size_t)(4 * 7) * kActChunkBytes, s_act, 4 * kActChunkBytes);
-        bulk_commit();
-      }
-      store_pending = true;
-      tc_fence_before();
-      mbar_arrive(bar_act);
+      return dsig;
+    };
 
-      for (int i = 0; i < kMmaLayers; ++i) {
-        const int t = (kFull ? 8 : 6) - i;  // this epilogue produces G_t
-        mbar_wait(bar_acc, acc_it & 1);
-        ++acc_it;
-        tc_fence_after();
+    int tile = blockIdx.x;
+    float dsig = 0.f, dsig_next = 0.f;
+    if (kFull && tile < a.num_tiles) dsig_next = prologue(tile);
+    for (; tile < a.num_tiles; tile += gridDim.x) {
+      const int next = tile + gridDim.x;
+      uint8_t* g_tile = a.gstash + (size_t)tile * gstash_tile_bytes(kFull);
+      const uint32_t* mask_tile = a.masks + (size_t)tile * mask_tile_words(kFull);
+      if (kFull) {
+        dsig = dsig_next;
+      } else {
+        // s_act is both the last layer's output (being stored) and this prologue's destination
         if (et == 0) bulk_wait_read0();
         named_bar_sync(1, kDgEpiThreads);
+        dsig = prologue(tile);
+      }
+#pragma unroll 1
+      for (int i = 0; i < kMmaLayers; ++i, ++g) {
+        const int t = (kFull ? 8 : 6) - i;  // this epilogue produces G_t
         uint32_t mw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-        if (t < 8) {
-          const uint4 m4 = *reinterpret_cast<const uint4*>(mask_tile + ((size_t)t * 128 + row) * 8 + h * 4);
+        if (t < 8) {   // issued before the wait so that the load latency hides behind the MMAs
+          const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(mask_tile + ((size_t)t * 128 + row) * 8 + sub * 4));
           mw[0] = m4.x; mw[1] = m4.y; mw[2] = m4.z; mw[3] = m4.w;
         }
-        {
-          const RowSwz rsw(row);
-          const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma), act_s = smem_u32(s_act);
-          if (kFull && t == 7) epi_dgrad128<true>(t_row, h * 128, rsw, act_s, mw, dsig, wsig_s);
-          else epi_dgrad128<false>(t_row, h * 128, rsw, act_s, mw, dsig, wsig_s);
+        const uint32_t b = g & 1u;
+        mbar_wait(bar_acc + b, (g >> 1) & 1u);
+        tc_fence_after();
+        if (et == 0) bulk_wait_read0();   // the previous image store may still be reading s_act
+        named_bar_sync(1, kDgEpiThreads);
+        const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + b * 256;
+        const bool feed = t > 0;
+        uint32_t va[32], vb[32];
+        tmem_ld32(t_acc + sub * 32, va);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t(&v)[32] = (c & 1) ? vb : va;
+          uint32_t(&vn)[32] = (c & 1) ? va : vb;
+          tmem_ld_wait_dep(v);
+          if (c + 1 < 4) tmem_ld32(t_acc + (c + 1) * 64 + sub * 32, vn);
+          const int c0 = c * 64 + sub * 32;
+          const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
+          if (kFull && t == 7) epi_dgrad32<true>(v, c0, mw[c], dsig, wsig_s, rsw, chunk_s, sub * 4);
+          else epi_dgrad32<false>(v, c0, mw[c], dsig, wsig_s, rsw, chunk_s, sub * 4);
+          if (feed) signal(c);
         }
-        fence_async_smem();
+        if (!feed) fence_async_smem();
         named_bar_sync(1, kDgEpiThreads);
         if (et == 0) {
           const int slot = (t == 8) ? kGstashG8 : 4 * t;
           bulk_s2g(g_tile + (size_t)slot * kActChunkBytes, s_act, 4 * kActChunkBytes);
           bulk_commit();
         }
-        if (t > 0) {
-          tc_fence_before();
-          mbar_arrive(bar_act);
-        }
+        // full mode: s_pro is free once this tile's first GEMM is done -> stage the next tile's G9 now
+        if (kFull && i == 0 && next < a.num_tiles) dsig_next = prologue(next);
       }
     }
     if (et == 0) bulk_wait_all0();
@@ -243,7 +284,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const DgradArg
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, 512);
   }
 }
 

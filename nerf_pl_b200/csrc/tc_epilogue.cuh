@@ -208,5 +208,54 @@ __device__ __forceinline__ void epi_dgrad128(uint32_t t_addr, int col0, const Ro
   }
 }
 
+// ---- chunk-granular epilogues (pipelined kernels): 32 accumulator columns already in registers ------
+// forward: x = acc + bias[c0..c0+31]; optional sign mask / fp32 dot with relu(x); (ReLU) + bf16; stored as
+// pieces p0..p0+3 of the thread's row in the 64-column SWIZZLE_128B chunk at chunk_saddr.
+template <bool kRelu, bool kMask, bool kDot>
+__device__ __forceinline__ void epi_fwd32(const uint32_t (&v)[32], int c0, uint32_t bias_saddr, uint32_t wdot_saddr,
+                                          const RowSwz& rs, uint32_t chunk_saddr, int p0, uint32_t& pos_mask, float& dot) {
+  uint32_t m = 0, pk[16];
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 b = ld_shared_f4(bias_saddr + (c0 + j) * 4);
+    const float x0 = __uint_as_float(v[j]) + b.x, x1 = __uint_as_float(v[j + 1]) + b.y;
+    const float x2 = __uint_as_float(v[j + 2]) + b.z, x3 = __uint_as_float(v[j + 3]) + b.w;
+    if (kMask) { m = push_sign(m, x0); m = push_sign(m, x1); m = push_sign(m, x2); m = push_sign(m, x3); }
+    if (kDot) {
+      const float4 w = ld_shared_f4(wdot_saddr + (c0 + j) * 4);
+      dot += fmaxf(x0, 0.f) * w.x + fmaxf(x1, 0.f) * w.y + fmaxf(x2, 0.f) * w.z + fmaxf(x3, 0.f) * w.w;
+    }
+    pk[j >> 1] = kRelu ? cvt_relu_bf16x2(x0, x1) : cvt_bf16x2(x0, x1);
+    pk[(j >> 1) + 1] = kRelu ? cvt_relu_bf16x2(x2, x3) : cvt_bf16x2(x2, x3);
+  }
+  if (kMask) pos_mask = ~m;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) st_shared_v4(chunk_saddr + rs.piece(p0 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+}
+
+// dgrad: G = (acc [+ dsig * w_sigma[c0..]]) masked by the forward's positive mask word.
+template <bool kAddSig>
+__device__ __forceinline__ void epi_dgrad32(const uint32_t (&v)[32], int c0, uint32_t pos_mask, float dsig,
+                                            uint32_t wsig_saddr, const RowSwz& rs, uint32_t chunk_saddr, int p0) {
+  uint32_t pk[16];
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    float f0 = __uint_as_float(v[j]), f1 = __uint_as_float(v[j + 1]), f2 = __uint_as_float(v[j + 2]),
+          f3 = __uint_as_float(v[j + 3]);
+    if (kAddSig) {
+      const float4 w = ld_shared_f4(wsig_saddr + (c0 + j) * 4);
+      f0 = fmaf(dsig, w.x, f0); f1 = fmaf(dsig, w.y, f1); f2 = fmaf(dsig, w.z, f2); f3 = fmaf(dsig, w.w, f3);
+    }
+    f0 = mask_bit(pos_mask, j) ? f0 : 0.f;
+    f1 = mask_bit(pos_mask, j + 1) ? f1 : 0.f;
+    f2 = mask_bit(pos_mask, j + 2) ? f2 : 0.f;
+    f3 = mask_bit(pos_mask, j + 3) ? f3 : 0.f;
+    pk[j >> 1] = cvt_bf16x2(f0, f1);
+    pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
+  }
+#pragma unroll
+  for (int p = 0; p < 4; ++p) st_shared_v4(chunk_saddr + rs.piece(p0 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+}
+
 }  // namespace tc
 }  // namespace nrf

@@ -62,7 +62,10 @@ constexpr size_t kPackedBytes = kPackedAuxOff + (size_t)AuxOffsets::count * 4;
 constexpr int kStashEnc = 0, kStashDir = 1, kStashH0 = 2, kStashFeat = 2 + 32, kStashMid = kStashFeat + 4;
 constexpr int kStashChunksFull = kStashMid + 2;   // 40
 constexpr int kStashChunksSigma = kStashFeat;     // 34 (no feat / dmid; dir slot unused)
-// ReLU sign masks: per tile, 8 hidden layers x 128 rows x 8 words, then dir layer 128 rows x 4 words
+// ReLU sign masks: per tile, 8 hidden layers x 128 rows x 8 words, then dir layer 128 rows x 4 words.
+// A thread of the pipelined kernels owns one row and the 32-column group `sub` (0/1) of every 64-column chunk c:
+// its words are stored contiguously, hidden layers word index = sub * 4 + c, dir layer = sub * 2 + c;
+// bit (31 - j) of a word <-> column c * 64 + sub * 32 + j positive (tc_epilogue.cuh: push_sign / mask_bit).
 constexpr int kMaskWordsFull = 8 * 128 * 8 + 128 * 4;
 constexpr int kMaskWordsSigma = 8 * 128 * 8;
 
