@@ -54,6 +54,7 @@ struct FwdArgs {
   float* rgb_out;
   uint8_t* stash;      // training only
   uint32_t* masks;     // training only
+  unsigned long long* dbg;  // optional per-CTA cycle counters (nrf_dbg_set_counters), null normally
 };
 
 // A-operand readiness barriers: act chunks 0..3, xyz encoding, direction encoding
@@ -120,41 +121,65 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
     }
   } else if (warp == 1) {
     // ===================== UMMA issuer =====================
+    // One thread; descriptors are precomputed and only their 14-bit start-address field is advanced, so the
+    // per-chunk issue cost stays well below the 512 cycles the four MMAs of a chunk execute for.
     if (lane == 0) {
       uint32_t stage = 0, ph = 0;
       uint32_t a_par = 0;   // bit i: parity of the next completion of bar_a[i] to wait for
+      long long w_a = 0, w_full = 0, t_begin = clock64();
       const uint32_t idesc256 = make_idesc_bf16(128, 256, 0, 0), idesc128 = make_idesc_bf16(128, 128, 0, 0);
+      const uint64_t enc_desc = make_desc_sw128(smem_u32(s_enc), 16, 1024);
+      const uint64_t dir_desc = make_desc_sw128(smem_u32(s_dir), 16, 1024);
+      const uint64_t act_desc = make_desc_sw128(smem_u32(s_act), 16, 1024);
+      const uint64_t ring_desc = make_desc_sw128(smem_u32(s_ring), 16, 1024);
+      auto wait_a = [&](int src) {
+        const long long t0 = a.dbg ? clock64() : 0;
+        mbar_wait(bar_a + src, (a_par >> src) & 1u);
+        a_par ^= 1u << src;
+        if (a.dbg) w_a += clock64() - t0;
+      };
+      // one K chunk (64 columns of A against one ring stage): 4 MMAs of K = 16
+      auto chunk = [&](uint64_t a_desc, uint32_t d_tmem, uint32_t idesc, bool first) {
+        const long long t0 = a.dbg ? clock64() : 0;
+        mbar_wait(bar_full + stage, ph);
+        if (a.dbg) w_full += clock64() - t0;
+        tc_fence_after();
+        const uint64_t b_desc = ring_desc + (uint64_t)(stage * (kChunkBytes256 >> 4));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (!first || k) ? 1u : 0u);
+        umma_commit(bar_empty + stage);
+        if (++stage == kStages) { stage = 0; ph ^= 1; }
+      };
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
 #pragma unroll 1
         for (int L = 0; L < kLayers; ++L) {
-          const int nchunks = (L == 0) ? 1 : ((L == 4 || L == 9) ? 5 : 4);
-          const uint32_t idesc = (L == 9) ? idesc128 : idesc256;
           const uint32_t d_tmem = tmem_base + (uint32_t)(L & 1) * 256;
-          for (int c = 0; c < nchunks; ++c) {
-            // which buffer / readiness barrier does this K chunk come from?
-            int src;  // 0..3 act chunk, kBarEnc, kBarDir
-            bool need_wait = true;
-            if (L == 0) src = kBarEnc;
-            else if (L == 4) { src = (c == 0) ? kBarEnc : c - 1; need_wait = c != 0; }  // enc was awaited at L0
-            else if (L == 9) src = (c < 4) ? c : kBarDir;
-            else src = c;
-            if (need_wait) {
-              mbar_wait(bar_a + src, (a_par >> src) & 1u);
-              a_par ^= 1u << src;
+          const uint32_t idesc = (L == 9) ? idesc128 : idesc256;
+          bool first = true;
+          if (L == 0 || L == 4) {          // the xyz encoding leads (skip connection: models/nerf.py:96-97)
+            if (L == 0) wait_a(kBarEnc);   // at layer 4 the same completion is still current
+            chunk(enc_desc, d_tmem, idesc, true);
+            first = false;
+          }
+          if (L != 0) {
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+              wait_a(c);
+              chunk(act_desc + (uint64_t)(c * (kActChunkBytes >> 4)), d_tmem, idesc, first);
+              first = false;
             }
-            mbar_wait(bar_full + stage, ph);
-            tc_fence_after();
-            const uint8_t* A = (src == kBarEnc) ? s_enc : (src == kBarDir ? s_dir : s_act + src * kActChunkBytes);
-            const uint32_t a_addr = smem_u32(A), b_addr = smem_u32(s_ring + stage * kChunkBytes256);
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_ss(d_tmem, make_desc_sw128(a_addr + k * 32, 16, 1024), make_desc_sw128(b_addr + k * 32, 16, 1024),
-                      idesc, (c | k) != 0);
-            umma_commit(bar_empty + stage);
-            if (++stage == kStages) { stage = 0; ph ^= 1; }
+          }
+          if (L == 9) {
+            wait_a(kBarDir);
+            chunk(dir_desc, d_tmem, idesc, false);
           }
           umma_commit(bar_acc + (L & 1));
         }
+      }
+      if (a.dbg) {
+        a.dbg[blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - t_begin);
+        a.dbg[blockIdx.x * 8 + 1] = (unsigned long long)w_a;
+        a.dbg[blockIdx.x * 8 + 2] = (unsigned long long)w_full;
       }
     }
   } else {
@@ -165,8 +190,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
     const RowSwz rsw(row);
     const uint32_t act_s = smem_u32(s_act), enc_s = smem_u32(s_enc), dir_s = smem_u32(s_dir);
     const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma);
-    const size_t tile_stash = stash_tile_bytes(kFull);
     uint32_t acc_par = 0;
+    long long w_acc = 0, t_begin = clock64();
 
     // this warp's part of an A-operand chunk is written: make it visible to the async proxy and tell the MMA thread
     auto signal = [&](int idx) {
@@ -190,7 +215,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
       if (kTrain) {
         named_bar_sync(1, kEpiThreads);
         if (et == 0) {
-          bulk_s2g(a.stash + (size_t)tile * tile_stash + (size_t)kStashEnc * kActChunkBytes, s_enc, kActChunkBytes);
+          bulk_s2g(a.stash + img_off(kStashEnc, 1, tile, a.num_tiles), s_enc, kActChunkBytes);
           bulk_commit();
         }
       }
@@ -210,7 +235,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
       if (kTrain) {
         named_bar_sync(1, kEpiThreads);
         if (et == 0) {
-          bulk_s2g(a.stash + (size_t)tile * tile_stash + (size_t)kStashDir * kActChunkBytes, s_dir, kActChunkBytes);
+          bulk_s2g(a.stash + img_off(kStashDir, 1, tile, a.num_tiles), s_dir, kActChunkBytes);
           bulk_commit();
         }
       }
@@ -223,14 +248,15 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
     }
     for (; tile < a.num_tiles; tile += gridDim.x) {
       const int next = tile + gridDim.x;
-      uint8_t* stash_tile = kTrain ? a.stash + (size_t)tile * tile_stash : nullptr;
       uint32_t* mask_tile = kTrain ? a.masks + (size_t)tile * mask_tile_words(kFull) : nullptr;
       const int64_t grow = (int64_t)tile * kTileM + row;
       const bool valid = grow < a.n_rows;
 #pragma unroll 1
       for (int L = 0; L < kLayers; ++L) {
         const uint32_t b = L & 1;
+        const long long tw0 = a.dbg ? clock64() : 0;
         mbar_wait(bar_acc + b, (acc_par >> b) & 1u);
+        if (a.dbg) w_acc += clock64() - tw0;
         acc_par ^= 1u << b;
         tc_fence_after();
         if (kTrain) {  // the stash store of the previous image may still be reading s_act
@@ -270,7 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
             named_bar_sync(1, kEpiThreads);
             if (et == 0) {
               const int slot = (L < 8) ? kStashH0 + 4 * L : kStashFeat;
-              bulk_s2g(stash_tile + (size_t)slot * kActChunkBytes, s_act, 4 * kActChunkBytes);
+              bulk_s2g(a.stash + img_off(slot, 4, tile, a.num_tiles), s_act, 4 * kActChunkBytes);
               bulk_commit();
             }
           }
@@ -329,7 +355,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
             fence_async_smem();
             named_bar_sync(1, kEpiThreads);
             if (et == 0) {
-              bulk_s2g(stash_tile + (size_t)kStashMid * kActChunkBytes, s_act, 2 * kActChunkBytes);
+              bulk_s2g(a.stash + img_off(kStashMid, 2, tile, a.num_tiles), s_act, 2 * kActChunkBytes);
               bulk_commit();
             }
           }
@@ -340,6 +366,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
       }
     }
     if (kTrain && et == 0) bulk_wait_all0();
+    if (a.dbg && et == 0) {
+      a.dbg[blockIdx.x * 8 + 4] = (unsigned long long)(clock64() - t_begin);
+      a.dbg[blockIdx.x * 8 + 5] = (unsigned long long)w_acc;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -372,6 +402,10 @@ static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
 using namespace nrf;
 using namespace nrf::tc;
 
+static unsigned long long* g_dbg_counters = nullptr;
+// Diagnostics: device buffer of >= 8 * gridDim 64-bit counters filled by the next forward launches (null = off).
+extern "C" void nrf_dbg_set_counters(void* dev_ptr) { g_dbg_counters = static_cast<unsigned long long*>(dev_ptr); }
+
 extern "C" size_t nrf_mlp_tc_stash_bytes(int64_t rows, int sigma_only) {
   if (rows <= 0) return 0;
   const size_t tiles = (size_t)((rows + kTileM - 1) / kTileM);
@@ -392,6 +426,7 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
   a.rays = rays; a.z = z; a.n_rows = rows; a.S = n_samples;
   a.num_tiles = (int)((rows + kTileM - 1) / kTileM);
   a.sigma_out = sigma_out; a.rgb_out = rgb_out;
+  a.dbg = g_dbg_counters;
   cudaStream_t st = as_stream(stream);
   if (stash != nullptr) {
     const size_t need = nrf_mlp_tc_stash_bytes(rows, sigma_only);

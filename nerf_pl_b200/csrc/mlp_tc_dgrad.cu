@@ -147,7 +147,6 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
     //   full mode : G9 -> s_pro (2 chunks), also writes dpre and the G9 image
     //   sigma-only: G7 = d_sigma * w_sigma (x) relu'(h7) -> s_act (4 chunks), also writes the G7 image
     auto prologue = [&](int tile) -> float {
-      uint8_t* g_tile = a.gstash + (size_t)tile * gstash_tile_bytes(kFull);
       const uint32_t* mask_tile = a.masks + (size_t)tile * mask_tile_words(kFull);
       const int64_t grow = (int64_t)tile * kTileM + row;
       const bool valid = grow < a.n_rows;
@@ -191,7 +190,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
         signal(kDgBarPro);
         named_bar_sync(1, kDgEpiThreads);
         if (et == 0) {
-          bulk_s2g(g_tile + (size_t)kGstashG9 * kActChunkBytes, s_pro, 2 * kActChunkBytes);
+          bulk_s2g(a.gstash + img_off(kGstashG9, 2, tile, a.num_tiles), s_pro, 2 * kActChunkBytes);
           bulk_commit();
         }
       } else {
@@ -216,7 +215,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
         }
         named_bar_sync(1, kDgEpiThreads);
         if (et == 0) {
-          bulk_s2g(g_tile + (size_t)(4 * 7) * kActChunkBytes, s_act, 4 * kActChunkBytes);
+          bulk_s2g(a.gstash + img_off(4 * 7, 4, tile, a.num_tiles), s_act, 4 * kActChunkBytes);
           bulk_commit();
         }
       }
@@ -228,7 +227,6 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
     if (kFull && tile < a.num_tiles) dsig_next = prologue(tile);
     for (; tile < a.num_tiles; tile += gridDim.x) {
       const int next = tile + gridDim.x;
-      uint8_t* g_tile = a.gstash + (size_t)tile * gstash_tile_bytes(kFull);
       const uint32_t* mask_tile = a.masks + (size_t)tile * mask_tile_words(kFull);
       if (kFull) {
         dsig = dsig_next;
@@ -271,7 +269,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
         named_bar_sync(1, kDgEpiThreads);
         if (et == 0) {
           const int slot = (t == 8) ? kGstashG8 : 4 * t;
-          bulk_s2g(g_tile + (size_t)slot * kActChunkBytes, s_act, 4 * kActChunkBytes);
+          bulk_s2g(a.gstash + img_off(slot, 4, tile, a.num_tiles), s_act, 4 * kActChunkBytes);
           bulk_commit();
         }
         // full mode: s_pro is free once this tile's first GEMM is done -> stage the next tile's G9 now

@@ -17,6 +17,7 @@
 // HBM-bound: ~10 KB/sample of images are read exactly once.
 // fp32 atomics make the summation order (not the values beyond rounding) run-dependent.
 #include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "tc_layout.cuh"
@@ -40,6 +41,8 @@ struct WgradJob {
   int a_slot, a_chunks;        // G image: first chunk slot in the G stash; 4 (N_out=256), 2 (N_out=128) or 0 (side work only)
   int b_n, b_mma;              // X chunks loaded / of which take part in the MMA (rest: side work only)
   int b_slot[kWgBSlots];       // forward-stash chunk slot of each X chunk
+  int b_img[kWgBSlots];        // first slot of the image that chunk belongs to
+  int b_imgn[kWgBSlots];       // chunks in that image
   int b_valid[kWgBSlots];      // per MMA X chunk: valid columns (destination column offset = 64 * index)
   float* dW; int ld;           // destination (row = n_out)
   float* db;                   // bias gradient = column sums of G, or null
@@ -51,12 +54,13 @@ struct WgradArgs {
   WgradJob jobs[kWgMaxJobs];
   int n_jobs, total_units, num_tiles;
   int64_t n_rows;
-  const uint8_t* xstash; size_t x_tile_bytes;
-  const uint8_t* gstash; size_t g_tile_bytes;
+  const uint8_t* xstash;
+  const uint8_t* gstash;
   const float* d_sigma;        // (rows)
   const float* dpre;           // (tiles*128, 4)
   float* dW_sigma; float* db_sigma; float* dW_rgb; float* db_rgb;
   int* unit_counter;           // zeroed before launch
+  int dbg_flags;               // experiments only (NRF_DBG_FLAGS): 1 = skip side work, 2 = skip MMAs
 };
 
 // two adjacent bf16 columns (2*cp, 2*cp+1) of row r of a 64-column SWIZZLE_128B slice
@@ -80,7 +84,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
   uint64_t* bar_uq_full = bars + 2 * kWgStages + 2;   // [2] unit id published (producer -> MMA, side)
   uint64_t* bar_uq_empty = bars + 2 * kWgStages + 4;  // [2] unit id consumed
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 2 * kWgStages + 6);
-  volatile int* s_unit = reinterpret_cast<volatile int*>(s_tmem + 1);  // [2]
+  volatile int* s_unit = reinterpret_cast<volatile int*>(s_tmem + 1);  // [2] unit queue, [2] = scratch
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
@@ -133,15 +137,16 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       size_t tile_stride = 0;
       uint32_t dst_off = 0;
       if (lane < a_chunks) {
-        src = a.gstash + (size_t)(job.a_slot + lane) * kActChunkBytes;
-        tile_stride = a.g_tile_bytes;
+        src = a.gstash + img_off(job.a_slot, a_chunks, t0, a.num_tiles) + (size_t)lane * kActChunkBytes;
+        tile_stride = (size_t)a_chunks * kActChunkBytes;
         dst_off = lane * kWgSlice;
       } else if (lane < n_copies) {
-        src = a.xstash + (size_t)job.b_slot[lane - a_chunks] * kActChunkBytes;
-        tile_stride = a.x_tile_bytes;
-        dst_off = (kWgASlots + lane - a_chunks) * kWgSlice;
+        const int bi = lane - a_chunks;
+        src = a.xstash + img_off(job.b_img[bi], job.b_imgn[bi], t0, a.num_tiles) +
+              (size_t)(job.b_slot[bi] - job.b_img[bi]) * kActChunkBytes;
+        tile_stride = (size_t)job.b_imgn[bi] * kActChunkBytes;
+        dst_off = (kWgASlots + bi) * kWgSlice;
       }
-      src += (size_t)t0 * tile_stride;
       const uint32_t bytes = (uint32_t)n_copies * kWgSlice;
       for (int s = 0; s < n_stage; ++s, ++it) {
         const uint32_t stage = it % kWgStages, ph = (it / kWgStages) & 1;
@@ -161,7 +166,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
           mbar_wait(bar_drained, (uq - 1) & 1);
           tc_fence_after();
         }
-        const int halves = a_chunks >> 1;
+        const int halves = (a.dbg_flags & 2) ? 0 : a_chunks >> 1;
         const int n_main = job.b_mma > 4 ? 4 : job.b_mma;
         const uint32_t idesc_main = make_idesc_bf16(128, 64 * n_main, 1, 1);
         const uint32_t idesc_tail = make_idesc_bf16(128, 64, 1, 1);
@@ -195,67 +200,135 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       }
     } else {
       // ---------------- side warps: column sums + head gradients, then the accumulator flush ----------------
+      // A thread owns ONE logical 8-column block cb of ONE slice k and a few rows of every stage: LDS.128 per row
+      // (physical piece = cb ^ (row & 7)), register accumulators per column, so the end-of-unit reduction is two
+      // shuffles and a handful of atomics.  All loads of a stage are issued first and the stage is released
+      // before the arithmetic.
       const int t = threadIdx.x - 64;
-      const int cp = t & 31;                 // column pair within a 64-column slice
-      float b0 = 0.f, b1 = 0.f;              // bias partial sums (columns 2cp, 2cp+1 of G slice `bch`)
-      float h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f, h4 = 0.f, h5 = 0.f, hb0 = 0.f, hb1 = 0.f, hb2 = 0.f;
-      const int bch = (t >> 5) & 3, brh = t >> 7;            // bias / sigma head: slice, 16-row half
-      const int rch = (t >> 5) & 1, rrq = t >> 6;            // rgb head: slice, 8-row quarter
-      const bool do_bias = job.db != nullptr && bch < a_chunks;
-      const int side = job.side;
+      const int cb = t & 7, rql = (t >> 3) & 3, sw = t >> 5;
+      const bool do_bias = job.db != nullptr && !(a.dbg_flags & 1);
+      const int side = (a.dbg_flags & 1) ? 0 : job.side;
+      // bias / sigma head: slice k4 = sw & 3, rows r4 .. r4+3;  rgb head: slice k2 = sw & 1, rows r2, r2+1
+      const int k4 = sw & 3, r4 = ((sw >> 2) * 4 + rql) * 4;
+      const int k2 = sw & 1, r2 = ((sw >> 1) * 4 + rql) * 2;
+      uint32_t off4[4], off2[2];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) off4[i] = (uint32_t)((r4 + i) * 128 + ((cb ^ ((r4 + i) & 7)) << 4));
+#pragma unroll
+      for (int i = 0; i < 2; ++i) off2[i] = (uint32_t)((r2 + i) * 128 + ((cb ^ ((r2 + i) & 7)) << 4));
+      const bool bias_on = do_bias && k4 < a_chunks;
+      float bs[8], hs[8], hg[8], hbv[8], hb0 = 0.f, hb1 = 0.f, hb2 = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { bs[e] = 0.f; hs[e] = 0.f; hg[e] = 0.f; hbv[e] = 0.f; }
+      auto unpack = [](const uint4& w, float (&f)[8]) {
+        f[0] = __uint_as_float(w.x << 16); f[1] = __uint_as_float(w.x & 0xffff0000u);
+        f[2] = __uint_as_float(w.y << 16); f[3] = __uint_as_float(w.y & 0xffff0000u);
+        f[4] = __uint_as_float(w.z << 16); f[5] = __uint_as_float(w.z & 0xffff0000u);
+        f[6] = __uint_as_float(w.w << 16); f[7] = __uint_as_float(w.w & 0xffff0000u);
+      };
       for (int s = 0; s < n_stage; ++s, ++it) {
         const int tile = t0 + (s >> 2), rs = s & 3;
         const uint32_t stage = it % kWgStages, ph = (it / kWgStages) & 1;
+        const int64_t row0 = (int64_t)tile * kTileM + rs * kWgSliceRows;
+        float ds[4] = {0.f, 0.f, 0.f, 0.f};
+        float4 dp[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+        if (side == 1) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ds[i] = (row0 + r4 + i < a.n_rows) ? __ldg(a.d_sigma + row0 + r4 + i) : 0.f;
+        } else if (side == 2) {
+#pragma unroll
+          for (int i = 0; i < 2; ++i) dp[i] = __ldg(reinterpret_cast<const float4*>(a.dpre) + row0 + r2 + i);
+        }
         mbar_wait(bar_full + stage, ph);
         const uint8_t* st = smem + stage * kWgStageBytes;
-        if (do_bias) {
-          const uint8_t* sl = st + bch * kWgSlice;
+        uint4 gw[4], xw[4];
+        uint32_t dep = 0;
+        if (bias_on) {
 #pragma unroll
-          for (int r = 0; r < 16; ++r) {
-            const float2 g = ld_img2(sl, brh * 16 + r, cp);
-            b0 += g.x; b1 += g.y;
+          for (int i = 0; i < 4; ++i) { gw[i] = *reinterpret_cast<const uint4*>(st + k4 * kWgSlice + off4[i]); dep ^= gw[i].w; }
+        }
+        if (side == 1) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            xw[i] = *reinterpret_cast<const uint4*>(st + (kWgASlots + job.side_off + k4) * kWgSlice + off4[i]);
+            dep ^= xw[i].w;
+          }
+        } else if (side == 2) {
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            xw[i] = *reinterpret_cast<const uint4*>(st + (kWgASlots + job.side_off + k2) * kWgSlice + off2[i]);
+            dep ^= xw[i].w;
+          }
+        }
+        // every load above must have RETURNED before the stage goes back to the async-proxy producer: a (never
+        // taken) store that depends on all loaded words keeps the scoreboard wait ahead of the arrive
+        if (dep == 0x5bd1e995u) s_unit[2] = (int)dep;   // s_unit[2]: scratch word nobody reads
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + stage);
+        float f[8];
+        if (bias_on) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            unpack(gw[i], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) bs[e] += f[e];
           }
         }
         if (side == 1) {
-          const uint8_t* sl = st + (kWgASlots + job.side_off + bch) * kWgSlice;
-          const int64_t r0 = (int64_t)tile * kTileM + rs * kWgSliceRows + brh * 16;
 #pragma unroll
-          for (int r = 0; r < 16; ++r) {
-            const float ds = (r0 + r < a.n_rows) ? __ldg(a.d_sigma + r0 + r) : 0.f;
-            const float2 x = ld_img2(sl, brh * 16 + r, cp);
-            h0 += ds * x.x; h1 += ds * x.y;
-            hb0 += ds;
+          for (int i = 0; i < 4; ++i) {
+            unpack(xw[i], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) hs[e] = fmaf(ds[i], f[e], hs[e]);
+            hb0 += ds[i];
           }
         } else if (side == 2) {
-          const uint8_t* sl = st + (kWgASlots + job.side_off + rch) * kWgSlice;
-          const float4* dp = reinterpret_cast<const float4*>(a.dpre) + (size_t)tile * kTileM + rs * kWgSliceRows + rrq * 8;
 #pragma unroll
-          for (int r = 0; r < 8; ++r) {
-            const float4 d = __ldg(dp + r);
-            const float2 x = ld_img2(sl, rrq * 8 + r, cp);
-            h0 += d.x * x.x; h1 += d.x * x.y;
-            h2 += d.y * x.x; h3 += d.y * x.y;
-            h4 += d.z * x.x; h5 += d.z * x.y;
-            hb0 += d.x; hb1 += d.y; hb2 += d.z;
+          for (int i = 0; i < 2; ++i) {
+            unpack(xw[i], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              hs[e] = fmaf(dp[i].x, f[e], hs[e]);
+              hg[e] = fmaf(dp[i].y, f[e], hg[e]);
+              hbv[e] = fmaf(dp[i].z, f[e], hbv[e]);
+            }
+            hb0 += dp[i].x; hb1 += dp[i].y; hb2 += dp[i].z;
           }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_empty + stage);
       }
-      if (do_bias) {
-        atomicAdd(job.db + bch * 64 + 2 * cp, b0);
-        atomicAdd(job.db + bch * 64 + 2 * cp + 1, b1);
+      // reduce over the four row groups that live in one warp (lane bits 3, 4), then one atomic per column and warp
+      auto warp_rows_sum = [&](float v) {
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        return v;
+      };
+      if (do_bias) {   // warp-uniform (k4 depends on the warp only)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float v = warp_rows_sum(bs[e]);
+          if (rql == 0 && k4 < a_chunks) atomicAdd(job.db + k4 * 64 + cb * 8 + e, v);
+        }
       }
       if (side == 1) {
-        atomicAdd(a.dW_sigma + bch * 64 + 2 * cp, h0);
-        atomicAdd(a.dW_sigma + bch * 64 + 2 * cp + 1, h1);
-        if ((t & 127) == 0) atomicAdd(a.db_sigma, hb0);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float v = warp_rows_sum(hs[e]);
+          if (rql == 0) atomicAdd(a.dW_sigma + k4 * 64 + cb * 8 + e, v);
+        }
+        const float vb = warp_rows_sum(hb0);
+        if (k4 == 0 && lane == 0) atomicAdd(a.db_sigma, vb);   // cb = 0 lanes of slice-0 warps cover every row once
       } else if (side == 2) {
-        const int k = rch * 64 + 2 * cp;
-        atomicAdd(a.dW_rgb + k, h0); atomicAdd(a.dW_rgb + k + 1, h1);
-        atomicAdd(a.dW_rgb + 128 + k, h2); atomicAdd(a.dW_rgb + 128 + k + 1, h3);
-        atomicAdd(a.dW_rgb + 256 + k, h4); atomicAdd(a.dW_rgb + 256 + k + 1, h5);
-        if ((t & 63) == 0) { atomicAdd(a.db_rgb, hb0); atomicAdd(a.db_rgb + 1, hb1); atomicAdd(a.db_rgb + 2, hb2); }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float v0 = warp_rows_sum(hs[e]), v1 = warp_rows_sum(hg[e]), v2 = warp_rows_sum(hbv[e]);
+          if (rql == 0) {
+            atomicAdd(a.dW_rgb + k2 * 64 + cb * 8 + e, v0);
+            atomicAdd(a.dW_rgb + 128 + k2 * 64 + cb * 8 + e, v1);
+            atomicAdd(a.dW_rgb + 256 + k2 * 64 + cb * 8 + e, v2);
+          }
+        }
+        const float w0 = warp_rows_sum(hb0), w1 = warp_rows_sum(hb1), w2 = warp_rows_sum(hb2);
+        if (k2 == 0 && lane == 0) { atomicAdd(a.db_rgb, w0); atomicAdd(a.db_rgb + 1, w1); atomicAdd(a.db_rgb + 2, w2); }
       }
       // accumulator flush: thread = TMEM lane (n_out within the half); the two warp groups split the column blocks
       mbar_wait(bar_acc, uq & 1);
@@ -307,7 +380,14 @@ static void add_job(WgradArgs& a, int a_slot, int a_chunks, std::initializer_lis
   j = WgradJob{};
   j.a_slot = a_slot; j.a_chunks = a_chunks; j.b_n = (int)b_slots.size(); j.b_mma = b_mma;
   int i = 0;
-  for (int s : b_slots) j.b_slot[i++] = s;
+  for (int s : b_slots) {
+    j.b_slot[i] = s;
+    // image the chunk belongs to (tc_layout.cuh): enc, dir: 1 chunk; h_l, feat: 4; dmid: 2
+    if (s < kStashH0) { j.b_img[i] = s; j.b_imgn[i] = 1; }
+    else if (s < kStashMid) { j.b_img[i] = kStashH0 + ((s - kStashH0) / 4) * 4; j.b_imgn[i] = 4; }
+    else { j.b_img[i] = kStashMid; j.b_imgn[i] = 2; }
+    ++i;
+  }
   i = 0;
   for (int v : valid) j.b_valid[i++] = v;
   j.dW = dW; j.ld = ld; j.db = db; j.side = side; j.side_off = side_off;
@@ -317,9 +397,10 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
                         const float* d_sigma, const float* dpre, int64_t n_rows, int num_tiles, int* unit_counter,
                         cudaStream_t st) {
   WgradArgs a{};
+  { const char* e = getenv("NRF_DBG_FLAGS"); a.dbg_flags = e ? atoi(e) : 0; }
   a.num_tiles = num_tiles; a.n_rows = n_rows;
-  a.xstash = xstash; a.x_tile_bytes = stash_tile_bytes(full);
-  a.gstash = gstash; a.g_tile_bytes = gstash_tile_bytes(full);
+  a.xstash = xstash;
+  a.gstash = gstash;
   a.d_sigma = d_sigma; a.dpre = dpre;
   a.dW_sigma = g->sigma_w; a.db_sigma = g->sigma_b; a.dW_rgb = g->rgb_w; a.db_rgb = g->rgb_b;
   a.unit_counter = unit_counter;
@@ -343,17 +424,19 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
   } else {
     add_job(a, 0, 0, {h7, h7 + 1, h7 + 2, h7 + 3}, 0, {}, nullptr, 0, nullptr, 1, 0);  // sigma head (side work only)
   }
-  // units of about equal byte count, ~6 per SM in total; CTAs claim them dynamically
+  // units of about equal duration, ~8 per SM in total; CTAs claim them dynamically
   int dev = 0, sms = kNumSMs;
   NRF_CUDA(cudaGetDevice(&dev));
   NRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   double total_cost = 0;
-  for (int i = 0; i < a.n_jobs; ++i) total_cost += a.jobs[i].a_chunks + a.jobs[i].b_n;
-  const double unit_cost = std::max(1.0, (double)num_tiles * total_cost / (6.0 * sms));
+  // per-stage cost ~ bytes, with a floor: thin stages are latency- rather than bandwidth-paced
+  auto stage_cost = [](const WgradJob& j) { return std::max(5, j.a_chunks + j.b_n); };
+  for (int i = 0; i < a.n_jobs; ++i) total_cost += stage_cost(a.jobs[i]);
+  const double unit_cost = std::max(1.0, (double)num_tiles * total_cost / (((a.dbg_flags & 8) ? 2.0 : 8.0) * sms));
   int unit = 0;
   for (int i = 0; i < a.n_jobs; ++i) {
     WgradJob& j = a.jobs[i];
-    int tpu = (int)(unit_cost / (j.a_chunks + j.b_n) + 0.5);
+    int tpu = (int)(unit_cost / stage_cost(j) + 0.5);
     tpu = std::max(1, std::min(tpu, num_tiles));
     j.tiles_per_unit = tpu;
     j.n_units = (num_tiles + tpu - 1) / tpu;

@@ -77,6 +77,14 @@ __host__ __device__ inline size_t gstash_tile_bytes(bool full) { return (size_t)
 __host__ __device__ inline size_t stash_tile_bytes(bool full) {
   return (size_t)(full ? kStashChunksFull : kStashChunksSigma) * kActChunkBytes;
 }
+// Stash addressing is IMAGE-major: an image = the chunks one bulk store writes for one tile (enc 1, dir 1, h_l 4,
+// feat 4, dmid 2; G_l 4, G9 2), and all tiles' copies of an image are contiguous.  The wgrad kernel streams one
+// image (or two) over many tiles, so each of its streams walks a dense region of HBM (tools/stream_bench.py:
+// 6.6 TB/s versus 4.9 TB/s for the tile-major order).  slot_start = index of the image's first chunk.
+__host__ __device__ inline size_t img_off(int slot_start, int img_chunks, int tile, int num_tiles) {
+  return ((size_t)slot_start * (size_t)num_tiles + (size_t)tile * (size_t)img_chunks) * kActChunkBytes;
+}
+
 __host__ __device__ inline size_t mask_tile_words(bool full) { return full ? kMaskWordsFull : kMaskWordsSigma; }
 
 }  // namespace tc
