@@ -4,17 +4,18 @@
 // Persistent kernel, one CTA per SM, 128-row tiles of sample points; the layer chain is software
 // pipelined at 64-column (= one K chunk) granularity so the tensor pipe rarely waits for the epilogue:
 //   warp 0      weight producer: linear bulk copies (TMA engine) of pre-packed 32 KB weight chunks
-//               L2 -> 3-stage shared-memory ring, mbarrier complete_tx
+//               L2 -> 4-stage shared-memory ring, mbarrier complete_tx
 //   warp 1      UMMA issuer: tcgen05.mma kind::f16, M=128, N=256 (128 for the direction layer),
 //               K=16 x 4 per chunk, A and B from shared memory (SWIZZLE_128B K-major).  Two fp32
 //               accumulators in TMEM (2 x 256 columns) alternate between layers; the MMAs of layer
 //               L+1 over K chunk c start as soon as the epilogue of layer L has produced chunk c.
-//   warps 2-9   epilogue, chunk by chunk: tcgen05.ld (32 lanes x 32 columns per thread) -> +bias ->
-//               ReLU -> bf16 -> in place into the A-operand buffer -> per-chunk mbarrier; sigma / rgb
-//               heads as fp32 dot products on the accumulators; the encoding of the NEXT tile is written
-//               while layers 5..9 of the current one run (the xyz encoding buffer is free after layer
-//               4, the direction buffer after layer 9).  Training mode also streams the operand images
-//               + ReLU sign masks to the HBM stash with bulk stores.
+//   warps 2-17  epilogue (4 warps per TMEM lane quarter, 16 columns of every chunk each): tcgen05.ld ->
+//               +bias -> ReLU -> bf16 -> in place into the A-operand buffer -> per-chunk mbarrier;
+//               sigma / rgb heads as fp32 dot products on the accumulators.  One 16 KB buffer holds the
+//               xyz encoding (layers 0..4) and then the direction encoding (layer 9) of a tile; the NEXT
+//               tile's xyz encoding is written as soon as the last layer's MMAs are done, before that
+//               layer's own epilogue, so the next chain starts while the heads are still evaluated.
+//               Training mode also streams the operand images + ReLU sign masks to the HBM stash.
 // Roofline: tensor pipe (593 408 MAC/sample).  HBM traffic: 32 B/ray in, 16 B/sample
 // out (+5.3 KB/sample stash when training); weights (1.17 MB) stay L2 resident (measured L2 -> SMEM
 // bulk-copy rate with all 148 CTAs on the same blob: > 19 TB/s, tools/stream_bench.py).
@@ -27,21 +28,22 @@
 namespace nrf {
 namespace tc {
 
-constexpr int kStages = 3;
-constexpr int kEpiWarps = 8;
+constexpr int kStages = 4;
+constexpr int kEpiWarps = 16;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;
+constexpr int kThreadsInfer = 64 + kEpiThreads;
+constexpr int kThreadsTrain = kThreadsInfer + 32;   // + the stash store warp
 constexpr uint32_t kTmemCols = 512;
 
-// shared-memory map (offsets from a 1024-byte aligned base)
-constexpr uint32_t kSmEnc = 0;
-constexpr uint32_t kSmDir = kSmEnc + kActChunkBytes;
-constexpr uint32_t kSmAct = kSmDir + kActChunkBytes;
+// shared-memory map (dynamic shared memory is declared 1024-byte aligned; no slack is left for re-alignment)
+constexpr uint32_t kSmEnc = 0;                                    // xyz encoding, later direction encoding
+constexpr uint32_t kSmAct = kSmEnc + kActChunkBytes;
 constexpr uint32_t kSmRing = kSmAct + 4 * kActChunkBytes;
 constexpr uint32_t kSmAux = kSmRing + kStages * kChunkBytes256;
-constexpr uint32_t kSmScratch = kSmAux + AuxOffsets::count * 4;  // [2][128][4] floats
-constexpr uint32_t kSmBars = kSmScratch + 2 * 128 * 4 * 4;
+constexpr uint32_t kSmScratch = kSmAux + AuxOffsets::count * 4;  // [4][128][3] floats
+constexpr uint32_t kSmBars = kSmScratch + 4 * 128 * 3 * 4;
 constexpr uint32_t kSmTotal = kSmBars + 256;
+static_assert(kSmTotal <= 232448, "shared memory budget");
 
 struct FwdArgs {
   const uint8_t* packed;
@@ -57,15 +59,36 @@ struct FwdArgs {
   unsigned long long* dbg;  // optional per-CTA cycle counters (nrf_dbg_set_counters), null normally
 };
 
+#ifndef NRF_FWD_DEBUG
+#define NRF_FWD_DEBUG 0   // build with NVCC_EXTRA=-DNRF_FWD_DEBUG=1 for the cycle counters / timeline (tools/fwd_*.py)
+#endif
+// Debug timeline (CTA 0 only, when dbg != null): dbg[kTraceBase + role * kTraceCap + n] = clock64() of event n.
+constexpr int kTraceBase = 148 * 8, kTraceCap = 4096;
+#define NRF_TRACE(role, n)                                                                          \
+  do {                                                                                              \
+    if (NRF_FWD_DEBUG && a.dbg && blockIdx.x == 0 && (n) < kTraceCap) a.dbg[kTraceBase + (role) * kTraceCap + (n)++] = clock64(); \
+  } while (0)
+
+// Progress markers (debug build, dbg = PINNED HOST memory so that they survive a trapped launch): the last wait every
+// role of every CTA entered, dbg[kMarkBase + cta * 32 + slot] = code (tools/fwd_deadlock.py decodes them).
+constexpr int kMarkBase = kTraceBase + 4 * kTraceCap;
+#define NRF_MARK(slot, code)                                                                        \
+  do {                                                                                              \
+    if (NRF_FWD_DEBUG && a.dbg) ((volatile unsigned long long*)a.dbg)[kMarkBase + blockIdx.x * 32 + (slot)] = (unsigned long long)(code); \
+  } while (0)
+
 // A-operand readiness barriers: act chunks 0..3, xyz encoding, direction encoding
 constexpr int kBarEnc = 4, kBarDir = 5, kNumBarA = 6;
+// "stash store has read the buffer" barriers (training): act chunks 0..3, encoding buffer
+constexpr int kFreeEnc = 4, kNumBarFree = 5;
+// images nobody but the store warp reads (a tile's last layer; dmid) are announced on barriers of their own: a parity
+// wait only tells "one completion behind" from "up to date", so every waiter must consume every completion of a barrier
+constexpr int kNumBarS = 4;
 
 template <bool kFull, bool kTrain>
-__global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_constant__ FwdArgs a) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+__global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp_fwd_kernel(const __grid_constant__ FwdArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* s_enc = smem + kSmEnc;
-  uint8_t* s_dir = smem + kSmDir;
   uint8_t* s_act = smem + kSmAct;
   uint8_t* s_ring = smem + kSmRing;
   float* s_aux = reinterpret_cast<float*>(smem + kSmAux);
@@ -75,26 +98,29 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
   uint64_t* bar_empty = bars + kStages;      // [kStages] weight chunk consumed
   uint64_t* bar_a = bars + 2 * kStages;      // [kNumBarA] A-operand chunk written (epilogue -> MMA)
   uint64_t* bar_acc = bar_a + kNumBarA;      // [2] accumulator complete (MMA -> epilogue)
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_acc + 2);
+  uint64_t* bar_free = bar_acc + 2;          // [kNumBarFree] stash store finished reading a buffer (store warp -> epilogue)
+  uint64_t* bar_s = bar_free + kNumBarFree;  // [kNumBarS] store-only image chunk written (epilogue -> store warp)
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_s + kNumBarS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kLayers = kFull ? 10 : 8;
   constexpr int kChunksPerTile = kFull ? kFwdChunksFull : kFwdChunksSigma;
 
   if (threadIdx.x == 0) {
+    if (smem_u32(smem) & 1023u) __trap();    // SWIZZLE_128B operands need the 1024-byte alignment
     for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
     for (int s = 0; s < kNumBarA; ++s) mbar_init(bar_a + s, kEpiWarps);
     mbar_init(bar_acc, 1);
     mbar_init(bar_acc + 1, 1);
+    for (int s = 0; s < kNumBarFree; ++s) mbar_init(bar_free + s, 1);
+    for (int s = 0; s < kNumBarS; ++s) mbar_init(bar_s + s, kEpiWarps);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(s_tmem, kTmemCols);
-  if (warp >= 2) {
+  if (warp >= 2 && warp < 2 + kEpiWarps) {
     const int et = threadIdx.x - 64;
     const float* gaux = reinterpret_cast<const float*>(a.packed + kPackedAuxOff);
     for (int i = et; i < AuxOffsets::count; i += kEpiThreads) s_aux[i] = gaux[i];
-    uint4* zp = reinterpret_cast<uint4*>(s_dir);  // direction chunk: columns 27..63 stay zero for the whole kernel
-    for (int i = et; i < (int)(kActChunkBytes / 16); i += kEpiThreads) zp[i] = make_uint4(0, 0, 0, 0);
   }
   tc_fence_before();
   __syncthreads();
@@ -105,9 +131,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
     // ===================== weight producer =====================
     if (lane == 0) {
       uint32_t stage = 0, ph = 0;
+      int tn0 = 0;
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
         for (int ci = 0; ci < kChunksPerTile; ++ci) {
+          NRF_MARK(0, 0x1000000 | (tile << 8) | ci);
           mbar_wait(bar_empty + stage, ph ^ 1);
+          NRF_TRACE(0, tn0);
           const bool half = ci >= kFwdChunksSigma + 4;
           const uint32_t bytes = half ? kChunkBytes128 : kChunkBytes256;
           const size_t off = half ? (size_t)(kFwdChunksSigma + 4) * kChunkBytes256 +
@@ -121,38 +150,54 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
     }
   } else if (warp == 1) {
     // ===================== UMMA issuer =====================
-    // One thread; descriptors are precomputed and only their 14-bit start-address field is advanced, so the
-    // per-chunk issue cost stays well below the 512 cycles the four MMAs of a chunk execute for.
+    // One thread; descriptors are precomputed and only their 14-bit start-address field is advanced.
     if (lane == 0) {
       uint32_t stage = 0, ph = 0;
       uint32_t a_par = 0;   // bit i: parity of the next completion of bar_a[i] to wait for
       long long w_a = 0, w_full = 0, t_begin = clock64();
+      int tn1 = 0;
       const uint32_t idesc256 = make_idesc_bf16(128, 256, 0, 0), idesc128 = make_idesc_bf16(128, 128, 0, 0);
       const uint64_t enc_desc = make_desc_sw128(smem_u32(s_enc), 16, 1024);
-      const uint64_t dir_desc = make_desc_sw128(smem_u32(s_dir), 16, 1024);
       const uint64_t act_desc = make_desc_sw128(smem_u32(s_act), 16, 1024);
       const uint64_t ring_desc = make_desc_sw128(smem_u32(s_ring), 16, 1024);
+      int mk = 0;   // (tile, layer) for the progress markers
       auto wait_a = [&](int src) {
-        const long long t0 = a.dbg ? clock64() : 0;
+        const long long t0 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
+        NRF_MARK(1, 0x2000000 | (mk << 4) | src);
         mbar_wait(bar_a + src, (a_par >> src) & 1u);
         a_par ^= 1u << src;
-        if (a.dbg) w_a += clock64() - t0;
+        if (NRF_FWD_DEBUG && a.dbg) w_a += clock64() - t0;
       };
-      // one K chunk (64 columns of A against one ring stage): 4 MMAs of K = 16
+      // Weight stages are awaited AHEAD of use, while the thread would otherwise idle waiting for the epilogue's
+      // first chunk: the per-chunk critical path is then one barrier wait + the issue of 4 MMAs (K = 16 each).
+      int ready = 0;   // upcoming ring stages already known to be full
+      auto prewait = [&](int n) {
+        uint32_t st = stage, p = ph;
+        for (int i = 0; i < ready; ++i) { if (++st == kStages) { st = 0; p ^= 1; } }
+        for (; ready < n; ++ready) {
+          mbar_wait(bar_full + st, p);
+          if (++st == kStages) { st = 0; p ^= 1; }
+        }
+      };
       auto chunk = [&](uint64_t a_desc, uint32_t d_tmem, uint32_t idesc, bool first) {
-        const long long t0 = a.dbg ? clock64() : 0;
-        mbar_wait(bar_full + stage, ph);
-        if (a.dbg) w_full += clock64() - t0;
+        const long long t0 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
+        NRF_TRACE(1, tn1);
+        NRF_MARK(1, 0x3000000 | (mk << 4));
+        if (ready == 0) mbar_wait(bar_full + stage, ph); else --ready;
+        NRF_TRACE(1, tn1);
+        if (NRF_FWD_DEBUG && a.dbg) w_full += clock64() - t0;
         tc_fence_after();
         const uint64_t b_desc = ring_desc + (uint64_t)(stage * (kChunkBytes256 >> 4));
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (!first || k) ? 1u : 0u);
         umma_commit(bar_empty + stage);
+        NRF_TRACE(1, tn1);
         if (++stage == kStages) { stage = 0; ph ^= 1; }
       };
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
 #pragma unroll 1
         for (int L = 0; L < kLayers; ++L) {
+          mk = (tile << 4) | L;
           const uint32_t d_tmem = tmem_base + (uint32_t)(L & 1) * 256;
           const uint32_t idesc = (L == 9) ? idesc128 : idesc256;
           bool first = true;
@@ -162,6 +207,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
             first = false;
           }
           if (L != 0) {
+            prewait(3);
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {
               wait_a(c);
@@ -169,29 +215,43 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
               first = false;
             }
           }
-          if (L == 9) {
+          if (L == 9) {                    // the direction encoding has replaced the xyz encoding in s_enc
             wait_a(kBarDir);
-            chunk(dir_desc, d_tmem, idesc, false);
+            chunk(enc_desc, d_tmem, idesc, false);
           }
           umma_commit(bar_acc + (L & 1));
         }
       }
-      if (a.dbg) {
+      if (NRF_FWD_DEBUG && a.dbg) {
         a.dbg[blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - t_begin);
         a.dbg[blockIdx.x * 8 + 1] = (unsigned long long)w_a;
         a.dbg[blockIdx.x * 8 + 2] = (unsigned long long)w_full;
       }
     }
-  } else {
+  } else if (warp < 2 + kEpiWarps) {
     // ===================== epilogue warps =====================
     const int et = threadIdx.x - 64;
-    const int q = warp & 3, sub = (warp - 2) >> 2;   // TMEM lane quarter; 32-column half of every 64-column chunk
+    const int q = warp & 3, sub = (warp - 2) >> 2;   // TMEM lane quarter; 16-column quarter of every 64-column chunk
     const int row = q * 32 + lane;
     const RowSwz rsw(row);
-    const uint32_t act_s = smem_u32(s_act), enc_s = smem_u32(s_enc), dir_s = smem_u32(s_dir);
+    const uint32_t act_s = smem_u32(s_act), enc_s = smem_u32(s_enc);
     const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma);
     uint32_t acc_par = 0;
     long long w_acc = 0, t_begin = clock64();
+    int tn2 = 0;
+    // training: every image written to s_act / s_enc is also copied to the stash by the store warp; a buffer may be
+    // overwritten once that copy has read it (bar_free).  bit i of `stored`: a copy of buffer i has been requested.
+    uint32_t free_par = 0, stored = 0;
+    int mk = 0;
+    auto acquire = [&](int buf) {
+      if (!kTrain) return;
+      if ((stored >> buf) & 1u) {
+        if (lane == 0) NRF_MARK(warp, 0x4000000 | (mk << 4) | buf);
+        mbar_wait(bar_free + buf, (free_par >> buf) & 1u);
+        free_par ^= 1u << buf;
+      }
+      stored |= 1u << buf;
+    };
 
     // this warp's part of an A-operand chunk is written: make it visible to the async proxy and tell the MMA thread
     auto signal = [&](int idx) {
@@ -200,7 +260,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_a + idx);
     };
-    // positional encoding of a tile's sample points -> s_enc (thread (er, part) fills 32 columns of row er)
+    auto signal_store = [&](int c) {   // an image chunk only the store warp reads
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_s + c);
+    };
+    // positional encoding of a tile's sample points -> s_enc (thread (er, part) fills 16 columns of row er)
     auto encode_xyz = [&](int tile) {
       const int er = et & 127, part = et >> 7;
       int64_t gr = (int64_t)tile * kTileM + er;
@@ -210,42 +275,26 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
       float p[3];
 #pragma unroll
       for (int c = 0; c < 3; ++c) p[c] = sample_point(a.rays, ray, zv, c);
-      encode_store<10>(part, p, enc_s, er);
+      acquire(kFreeEnc);
+      encode_store16<10>(part, p, enc_s, er);
       signal(kBarEnc);
-      if (kTrain) {
-        named_bar_sync(1, kEpiThreads);
-        if (et == 0) {
-          bulk_s2g(a.stash + img_off(kStashEnc, 1, tile, a.num_tiles), s_enc, kActChunkBytes);
-          bulk_commit();
-        }
-      }
     };
+    // direction encoding of the same rows, into the same buffer (the xyz encoding is dead after layer 4)
     auto encode_dir = [&](int tile) {
       const int er = et & 127, part = et >> 7;
-      if (part == 0) {
-        int64_t gr = (int64_t)tile * kTileM + er;
-        if (gr >= a.n_rows) gr = a.n_rows - 1;
-        const int64_t ray = gr / a.S;
-        float d[3];
+      int64_t gr = (int64_t)tile * kTileM + er;
+      if (gr >= a.n_rows) gr = a.n_rows - 1;
+      const int64_t ray = gr / a.S;
+      float d[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) d[c] = __ldg(a.rays + ray * 8 + 3 + c);
-        encode_store<4>(0, d, dir_s, er);
-      }
+      for (int c = 0; c < 3; ++c) d[c] = __ldg(a.rays + ray * 8 + 3 + c);
+      acquire(kFreeEnc);
+      encode_store16<4>(part, d, enc_s, er);
       signal(kBarDir);
-      if (kTrain) {
-        named_bar_sync(1, kEpiThreads);
-        if (et == 0) {
-          bulk_s2g(a.stash + img_off(kStashDir, 1, tile, a.num_tiles), s_dir, kActChunkBytes);
-          bulk_commit();
-        }
-      }
     };
 
     int tile = blockIdx.x;
-    if (tile < a.num_tiles) {
-      encode_xyz(tile);
-      if (kFull) encode_dir(tile);
-    }
+    if (tile < a.num_tiles) encode_xyz(tile);
     for (; tile < a.num_tiles; tile += gridDim.x) {
       const int next = tile + gridDim.x;
       uint32_t* mask_tile = kTrain ? a.masks + (size_t)tile * mask_tile_words(kFull) : nullptr;
@@ -254,72 +303,79 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
 #pragma unroll 1
       for (int L = 0; L < kLayers; ++L) {
         const uint32_t b = L & 1;
-        const long long tw0 = a.dbg ? clock64() : 0;
+        const long long tw0 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
+        mk = (tile << 4) | L;
+        if (lane == 0) NRF_MARK(warp, 0x5000000 | (mk << 4));
         mbar_wait(bar_acc + b, (acc_par >> b) & 1u);
-        if (a.dbg) w_acc += clock64() - tw0;
+        if (NRF_FWD_DEBUG && a.dbg) w_acc += clock64() - tw0;
+        if (et == 0) NRF_TRACE(2, tn2);
         acc_par ^= 1u << b;
         tc_fence_after();
-        if (kTrain) {  // the stash store of the previous image may still be reading s_act
-          if (et == 0) bulk_wait_read0();
-          named_bar_sync(1, kEpiThreads);
-        }
         const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + b * 256;
         if (L < 9) {
           const bool feed = L + 1 < kLayers;   // the next layer's MMAs consume these chunks
           const uint32_t bias_s = smem_u32(s_aux + (L < 8 ? AuxOffsets::bias + L * 256 : AuxOffsets::bias_final));
-          uint32_t mw[4] = {0, 0, 0, 0};
+          uint32_t mreg = 0, mw0 = 0, mw1 = 0;
           float dot = 0.f;
-          uint32_t va[32], vb[32];
-          tmem_ld32(t_acc + sub * 32, va);
+          uint32_t va[16], vb[16];
+          tmem_ld16(t_acc + sub * 16, va);
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
-            uint32_t(&v)[32] = (c & 1) ? vb : va;
-            uint32_t(&vn)[32] = (c & 1) ? va : vb;
-            tmem_ld_wait_dep(v);
-            if (c + 1 < 4) tmem_ld32(t_acc + (c + 1) * 64 + sub * 32, vn);
-            const int c0 = c * 64 + sub * 32;
+            uint32_t(&v)[16] = (c & 1) ? vb : va;
+            uint32_t(&vn)[16] = (c & 1) ? va : vb;
+            tmem_ld_wait_dep16(v);
+            if (c + 1 < 4) tmem_ld16(t_acc + (c + 1) * 64 + sub * 16, vn);
+            const int c0 = c * 64 + sub * 16;
             const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-            if (L == 7) epi_fwd32<true, kTrain, true>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 4, mw[c], dot);
-            else if (L < 8) epi_fwd32<true, kTrain, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 4, mw[c], dot);
-            else epi_fwd32<false, false, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 4, mw[c], dot);
-            if (feed) signal(c);
+            acquire(c);
+            if (L == 7) epi_fwd16<true, kTrain, true>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
+            else if (L < 8) epi_fwd16<true, kTrain, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
+            else epi_fwd16<false, false, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
+            if (kTrain && (c & 1)) {
+              if (c == 1) mw0 = ~mreg; else mw1 = ~mreg;
+              mreg = 0;
+            }
+            if (feed) signal(c);             // the MMA thread (and, in training, the store warp) take it from here
+            else if (kTrain) signal_store(c);
+            if (et == 0) NRF_TRACE(2, tn2);
           }
           if (kTrain && L < 8)
-            *reinterpret_cast<uint4*>(mask_tile + ((size_t)L * 128 + row) * 8 + sub * 4) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+            *reinterpret_cast<uint2*>(mask_tile + ((size_t)L * 128 + row) * 8 + sub * 2) = make_uint2(mw0, mw1);
           if (L == 7) {
             s_scr[sub * 128 + row] = dot;
             named_bar_sync(2, kEpiThreads);
-            if (sub == 0 && valid) a.sigma_out[grow] = s_scr[row] + s_scr[128 + row] + s_aux[AuxOffsets::b_sigma];
+            if (sub == 0 && valid)
+              a.sigma_out[grow] = (s_scr[row] + s_scr[128 + row]) + (s_scr[256 + row] + s_scr[384 + row]) + s_aux[AuxOffsets::b_sigma];
           }
-          if (kTrain) {
-            if (!feed) fence_async_smem();
-            named_bar_sync(1, kEpiThreads);
-            if (et == 0) {
-              const int slot = (L < 8) ? kStashH0 + 4 * L : kStashFeat;
-              bulk_s2g(a.stash + img_off(slot, 4, tile, a.num_tiles), s_act, 4 * kActChunkBytes);
-              bulk_commit();
-            }
+          if (L == 4) {
+            if (kFull) encode_dir(tile);                        // s_enc: xyz encoding -> direction encoding
+            else if (next < a.num_tiles) encode_xyz(next);     // sigma-only: the buffer is free from here on
           }
         } else {
-          // direction layer: N = 128; rgb head on the fp32 accumulators (nerf.py:119-121)
+          // direction layer: N = 128; rgb head on the fp32 accumulators (nerf.py:119-121).
+          // Its MMAs are done, so s_enc is free: start the next tile's chain before evaluating the heads.
+          if (next < a.num_tiles) encode_xyz(next);
           float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-          uint32_t mwd[2] = {0, 0};
+          uint32_t mreg = 0;
           const uint32_t bdir_s = smem_u32(s_aux + AuxOffsets::bias_dir), wrgb_s = smem_u32(s_aux + AuxOffsets::w_rgb);
-          uint32_t va[32], vb[32];
-          tmem_ld32(t_acc + sub * 32, va);
-          tmem_ld32(t_acc + 64 + sub * 32, vb);
+          uint32_t va[16], vb[16];
+          tmem_ld16(t_acc + sub * 16, va);
+          tmem_ld16(t_acc + 64 + sub * 16, vb);
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
-            uint32_t(&v)[32] = c ? vb : va;
-            tmem_ld_wait_dep(v);
-            const int c0 = c * 64 + sub * 32;
-            uint32_t m = 0, pk[16];
+            uint32_t(&v)[16] = c ? vb : va;
+            tmem_ld_wait_dep16(v);
+            const int c0 = c * 64 + sub * 16;
+            uint32_t pk[8];
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
+            for (int j = 0; j < 16; j += 4) {
               const float4 bb = ld_shared_f4(bdir_s + (c0 + j) * 4);
               const float x0 = __uint_as_float(v[j]) + bb.x, x1 = __uint_as_float(v[j + 1]) + bb.y;
               const float x2 = __uint_as_float(v[j + 2]) + bb.z, x3 = __uint_as_float(v[j + 3]) + bb.w;
-              if (kTrain) { m = push_sign(m, x0); m = push_sign(m, x1); m = push_sign(m, x2); m = push_sign(m, x3); }
+              if (kTrain) {
+                mreg = push_sign(mreg, x0); mreg = push_sign(mreg, x1);
+                mreg = push_sign(mreg, x2); mreg = push_sign(mreg, x3);
+              }
               const float f0 = fmaxf(x0, 0.f), f1 = fmaxf(x1, 0.f), f2 = fmaxf(x2, 0.f), f3 = fmaxf(x3, 0.f);
               const float4 w0 = ld_shared_f4(wrgb_s + (c0 + j) * 4), w1 = ld_shared_f4(wrgb_s + (128 + c0 + j) * 4),
                            w2 = ld_shared_f4(wrgb_s + (256 + c0 + j) * 4);
@@ -331,45 +387,77 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
                 pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
               }
             }
-            mwd[c] = ~m;
             if (kTrain) {
               const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-#pragma unroll
-              for (int p = 0; p < 4; ++p)
-                st_shared_v4(chunk_s + rsw.piece(sub * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+              acquire(c);
+              st_shared_v4(chunk_s + rsw.piece(sub * 2), pk[0], pk[1], pk[2], pk[3]);
+              st_shared_v4(chunk_s + rsw.piece(sub * 2 + 1), pk[4], pk[5], pk[6], pk[7]);
+              signal_store(c);
             }
           }
-          if (kTrain) *reinterpret_cast<uint2*>(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + sub * 2) = make_uint2(mwd[0], mwd[1]);
-          float* sc = s_scr + (sub * 128 + row) * 4;
+          if (kTrain) mask_tile[8 * 128 * 8 + (size_t)row * 4 + sub] = ~mreg;
+          float* sc = s_scr + (sub * 128 + row) * 3;
           sc[0] = r0; sc[1] = r1; sc[2] = r2;
           named_bar_sync(2, kEpiThreads);
           if (sub == 0 && valid) {
-            const float* o = s_scr + (128 + row) * 4;
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-              const float pre = sc[c] + o[c] + s_aux[AuxOffsets::b_rgb + c];
+              const float pre = (s_scr[row * 3 + c] + s_scr[(128 + row) * 3 + c]) +
+                                (s_scr[(256 + row) * 3 + c] + s_scr[(384 + row) * 3 + c]) + s_aux[AuxOffsets::b_rgb + c];
               a.rgb_out[grow * 3 + c] = 1.0f / (1.0f + expf(-pre));
             }
           }
-          if (kTrain) {
-            fence_async_smem();
-            named_bar_sync(1, kEpiThreads);
-            if (et == 0) {
-              bulk_s2g(a.stash + img_off(kStashMid, 2, tile, a.num_tiles), s_act, 2 * kActChunkBytes);
-              bulk_commit();
-            }
-          }
         }
-        // the encodings of the next tile: s_enc is free once layer 4's MMAs are done, s_dir after layer 9's
-        if (L == 4 && next < a.num_tiles) encode_xyz(next);
-        if (kFull && L == 9 && next < a.num_tiles) encode_dir(next);
       }
     }
-    if (kTrain && et == 0) bulk_wait_all0();
-    if (a.dbg && et == 0) {
+    if (NRF_FWD_DEBUG && a.dbg && et == 0) {
       a.dbg[blockIdx.x * 8 + 4] = (unsigned long long)(clock64() - t_begin);
       a.dbg[blockIdx.x * 8 + 5] = (unsigned long long)w_acc;
     }
+  } else if (kTrain && lane == 0) {
+    // ===================== stash store warp (training) =====================
+    // One thread follows the epilogue's production order: as soon as a 16 KB operand image is complete (bar_a) it is
+    // bulk-copied to the stash; once the copy has read the buffer (one copy behind, so two are in flight) the
+    // epilogue may overwrite it (bar_free).
+    uint32_t s_par = 0;
+    int pending = -1;
+    int mk = 0;
+    auto store = [&](int bar_idx, int buf, const uint8_t* src, uint8_t* dst) {   // bar_idx >= 8: bar_s[bar_idx - 8]
+      NRF_MARK(18, 0x6000000 | (mk << 4) | bar_idx);
+      mbar_wait(bar_idx < 8 ? bar_a + bar_idx : bar_s + (bar_idx - 8), (s_par >> bar_idx) & 1u);
+      s_par ^= 1u << bar_idx;
+      bulk_s2g(dst, src, kActChunkBytes);
+      bulk_commit();
+      if (pending >= 0) {
+        bulk_wait_read1();
+        mbar_arrive(bar_free + pending);
+      }
+      pending = buf;
+    };
+    int tile = blockIdx.x;
+    if (tile < a.num_tiles) store(kBarEnc, kFreeEnc, s_enc, a.stash + img_off(kStashEnc, 1, tile, a.num_tiles));
+    for (; tile < a.num_tiles; tile += gridDim.x) {
+      const int next = tile + gridDim.x;
+#pragma unroll 1
+      for (int L = 0; L < kLayers; ++L) {
+        mk = (tile << 4) | L;
+        if (L < 9) {
+          uint8_t* dst = a.stash + img_off(L < 8 ? kStashH0 + 4 * L : kStashFeat, 4, tile, a.num_tiles);
+          const int bar0 = (L + 1 < kLayers) ? 0 : 8;
+          for (int c = 0; c < 4; ++c) store(bar0 + c, c, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes);
+          if (L == 4) {
+            if (kFull) store(kBarDir, kFreeEnc, s_enc, a.stash + img_off(kStashDir, 1, tile, a.num_tiles));
+            else if (next < a.num_tiles) store(kBarEnc, kFreeEnc, s_enc, a.stash + img_off(kStashEnc, 1, next, a.num_tiles));
+          }
+        } else {
+          if (next < a.num_tiles) store(kBarEnc, kFreeEnc, s_enc, a.stash + img_off(kStashEnc, 1, next, a.num_tiles));
+          uint8_t* dst = a.stash + img_off(kStashMid, 2, tile, a.num_tiles);
+          for (int c = 0; c < 2; ++c) store(8 + c, c, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes);
+        }
+      }
+    }
+    bulk_wait_all0();
+    NRF_MARK(18, 0x7000000);
   }
   tc_fence_before();
   __syncthreads();
@@ -382,7 +470,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_fwd_kernel(const __grid_const
 template <bool kFull, bool kTrain>
 static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
   static bool configured = false;
-  const int smem_bytes = (int)kSmTotal + 1024;
+  const int smem_bytes = (int)kSmTotal;
   if (!configured) {
     NRF_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<kFull, kTrain>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     configured = true;
@@ -391,7 +479,7 @@ static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
   NRF_CUDA(cudaGetDevice(&dev));
   NRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int grid = a.num_tiles < sms ? a.num_tiles : sms;
-  mlp_fwd_kernel<kFull, kTrain><<<grid, kThreads, smem_bytes, st>>>(a);
+  mlp_fwd_kernel<kFull, kTrain><<<grid, kTrain ? kThreadsTrain : kThreadsInfer, smem_bytes, st>>>(a);
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

@@ -21,16 +21,19 @@
 namespace nrf {
 namespace tc {
 
-constexpr int kDgStages = 3;
-constexpr int kDgEpiWarps = 8;
+constexpr int kDgStages = 4;
+constexpr int kDgEpiWarps = 16;
 constexpr int kDgEpiThreads = kDgEpiWarps * 32;
-constexpr int kDgThreads = 64 + kDgEpiThreads;
+constexpr int kDgThreads = 64 + kDgEpiThreads + 32;   // producer, UMMA issuer, epilogue warps, G-image store warp
 constexpr uint32_t kDgSmAct = 0;
 constexpr uint32_t kDgSmPro = kDgSmAct + 4 * kActChunkBytes;      // full mode: staging of the next tile's G9 (2 chunks)
 constexpr uint32_t kDgSmRing = kDgSmPro + 2 * kActChunkBytes;
 constexpr uint32_t kDgSmAux = kDgSmRing + kDgStages * kChunkBytes256;
-constexpr uint32_t kDgSmBars = kDgSmAux + AuxOffsets::count * 4;
+constexpr int kDgAuxFirst = AuxOffsets::w_sigma;                   // only the head weights are needed here
+constexpr int kDgAuxCount = AuxOffsets::count - kDgAuxFirst;
+constexpr uint32_t kDgSmBars = kDgSmAux + kDgAuxCount * 4;
 constexpr uint32_t kDgSmTotal = kDgSmBars + 256;
+static_assert(kDgSmTotal <= 232448, "shared memory budget");
 
 struct DgradArgs {
   const uint8_t* packed;
@@ -45,21 +48,26 @@ struct DgradArgs {
 };
 
 constexpr int kDgBarPro = 4, kDgNumBarA = 5;   // A-operand readiness: act chunks 0..3, G9 staging
+constexpr int kDgNumBarFree = 5;               // same buffers: the G-image store has read them
+// G0 (nobody but the store warp reads it) is announced on barriers of its own: a parity wait only tells "one completion
+// behind" from "up to date", so every waiter must consume every completion of a barrier
+constexpr int kDgNumBarS = 4;
 
 template <bool kFull>
 __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_constant__ DgradArgs a) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* s_act = smem + kDgSmAct;
   uint8_t* s_pro = smem + kDgSmPro;
   uint8_t* s_ring = smem + kDgSmRing;
-  float* s_aux = reinterpret_cast<float*>(smem + kDgSmAux);
+  float* s_aux = reinterpret_cast<float*>(smem + kDgSmAux) - kDgAuxFirst;   // indexed with AuxOffsets (>= w_sigma)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kDgSmBars);
   uint64_t* bar_full = bars;
   uint64_t* bar_empty = bars + kDgStages;
   uint64_t* bar_a = bars + 2 * kDgStages;     // [kDgNumBarA]
   uint64_t* bar_acc = bar_a + kDgNumBarA;     // [2]
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_acc + 2);
+  uint64_t* bar_free = bar_acc + 2;           // [kDgNumBarFree]
+  uint64_t* bar_s = bar_free + kDgNumBarFree;  // [kDgNumBarS]
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar_s + kDgNumBarS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kMmaLayers = kFull ? 9 : 7;
@@ -67,16 +75,19 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
   constexpr int kChunks = kBwdChunks - kFirstChunk;
 
   if (threadIdx.x == 0) {
+    if (smem_u32(smem) & 1023u) __trap();
     for (int s = 0; s < kDgStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
     for (int s = 0; s < kDgNumBarA; ++s) mbar_init(bar_a + s, kDgEpiWarps);
     mbar_init(bar_acc, 1);
     mbar_init(bar_acc + 1, 1);
+    for (int s = 0; s < kDgNumBarFree; ++s) mbar_init(bar_free + s, 1);
+    for (int s = 0; s < kDgNumBarS; ++s) mbar_init(bar_s + s, kDgEpiWarps);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(s_tmem, 512);
-  if (warp >= 2) {
+  if (warp >= 2 && warp < 2 + kDgEpiWarps) {
     const float* gaux = reinterpret_cast<const float*>(a.packed + kPackedAuxOff);
-    for (int i = threadIdx.x - 64; i < AuxOffsets::count; i += kDgEpiThreads) s_aux[i] = gaux[i];
+    for (int i = kDgAuxFirst + threadIdx.x - 64; i < AuxOffsets::count; i += kDgEpiThreads) s_aux[i] = gaux[i];
   }
   tc_fence_before();
   __syncthreads();
@@ -101,26 +112,39 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
     if (lane == 0) {
       uint32_t stage = 0, ph = 0, a_par = 0, g = 0;   // g: running layer counter (accumulators alternate across tiles too)
       const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
+      const uint64_t act_desc = make_desc_sw128(smem_u32(s_act), 16, 1024);
+      const uint64_t pro_desc = make_desc_sw128(smem_u32(s_pro), 16, 1024);
+      const uint64_t ring_desc = make_desc_sw128(smem_u32(s_ring), 16, 1024);
+      // weight stages are awaited ahead of use, while the thread would otherwise idle waiting for the epilogue
+      int ready = 0;
+      auto prewait = [&](int n) {
+        uint32_t st = stage, p = ph;
+        for (int i = 0; i < ready; ++i) { if (++st == kDgStages) { st = 0; p ^= 1; } }
+        for (; ready < n; ++ready) {
+          mbar_wait(bar_full + st, p);
+          if (++st == kDgStages) { st = 0; p ^= 1; }
+        }
+      };
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
 #pragma unroll 1
         for (int i = 0; i < kMmaLayers; ++i, ++g) {
           const bool from_pro = kFull && i == 0;
           const int nchunks = from_pro ? 2 : 4;
           const uint32_t d_tmem = tmem_base + (g & 1u) * 256;
+          prewait(from_pro ? 2 : 3);
+#pragma unroll 1
           for (int c = 0; c < nchunks; ++c) {
             const int src = from_pro ? kDgBarPro : c;
             if (!from_pro || c == 0) {
               mbar_wait(bar_a + src, (a_par >> src) & 1u);
               a_par ^= 1u << src;
             }
-            mbar_wait(bar_full + stage, ph);
+            if (ready == 0) mbar_wait(bar_full + stage, ph); else --ready;
             tc_fence_after();
-            const uint32_t a_addr = smem_u32((from_pro ? s_pro : s_act) + c * kActChunkBytes);
-            const uint32_t b_addr = smem_u32(s_ring + stage * kChunkBytes256);
+            const uint64_t a_desc = (from_pro ? pro_desc : act_desc) + (uint64_t)(c * (kActChunkBytes >> 4));
+            const uint64_t b_desc = ring_desc + (uint64_t)(stage * (kChunkBytes256 >> 4));
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_ss(d_tmem, make_desc_sw128(a_addr + k * 32, 16, 1024), make_desc_sw128(b_addr + k * 32, 16, 1024),
-                      idesc, (c | k) != 0);
+            for (int k = 0; k < 4; ++k) umma_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (c | k) != 0);
             umma_commit(bar_empty + stage);
             if (++stage == kDgStages) { stage = 0; ph ^= 1; }
           }
@@ -128,14 +152,24 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
         }
       }
     }
-  } else {
+  } else if (warp < 2 + kDgEpiWarps) {
     const int et = threadIdx.x - 64;
-    const int q = warp & 3, sub = (warp - 2) >> 2;   // TMEM lane quarter; 32-column half of every 64-column chunk
+    const int q = warp & 3, sub = (warp - 2) >> 2;   // TMEM lane quarter; 16-column quarter of every 64-column chunk
     const int row = q * 32 + lane;
     const RowSwz rsw(row);
     const uint32_t act_s = smem_u32(s_act), pro_s = smem_u32(s_pro);
     const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma), wrgb_s = smem_u32(s_aux + AuxOffsets::w_rgb);
     uint32_t g = 0;   // running layer counter, mirrors the UMMA issuer
+    // Every image written to s_act / s_pro is also copied to the G stash by the store warp; a buffer may be overwritten
+    // once that copy has read it (bar_free).  bit i of `stored`: a copy of buffer i has been requested.
+    uint32_t free_par = 0, stored = 0;
+    auto acquire = [&](int buf) {
+      if ((stored >> buf) & 1u) {
+        mbar_wait(bar_free + buf, (free_par >> buf) & 1u);
+        free_par ^= 1u << buf;
+      }
+      stored |= 1u << buf;
+    };
 
     auto signal = [&](int idx) {
       fence_async_smem();
@@ -161,62 +195,51 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
           }
         }
         if (sub == 0) *reinterpret_cast<float4*>(a.dpre + ((size_t)tile * kTileM + row) * 4) = make_float4(dp[0], dp[1], dp[2], 0.f);
-        const uint2 mw = *reinterpret_cast<const uint2*>(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + sub * 2);
+        const uint32_t m = __ldg(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + sub);
+        acquire(kDgBarPro);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-          const uint32_t m = c ? mw.y : mw.x;
-          uint32_t pk[16];
+          uint32_t pk[8];
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const int col = c * 64 + sub * 32 + j;
+          for (int j = 0; j < 16; j += 4) {
+            const int col = c * 64 + sub * 16 + j;
             const float4 w0 = ld_shared_f4(wrgb_s + col * 4), w1 = ld_shared_f4(wrgb_s + (128 + col) * 4),
                          w2 = ld_shared_f4(wrgb_s + (256 + col) * 4);
             float f0 = dp[0] * w0.x + dp[1] * w1.x + dp[2] * w2.x;
             float f1 = dp[0] * w0.y + dp[1] * w1.y + dp[2] * w2.y;
             float f2 = dp[0] * w0.z + dp[1] * w1.z + dp[2] * w2.z;
             float f3 = dp[0] * w0.w + dp[1] * w1.w + dp[2] * w2.w;
-            f0 = mask_bit(m, j) ? f0 : 0.f;
-            f1 = mask_bit(m, j + 1) ? f1 : 0.f;
-            f2 = mask_bit(m, j + 2) ? f2 : 0.f;
-            f3 = mask_bit(m, j + 3) ? f3 : 0.f;
+            f0 = mask_bit16(m, c, j) ? f0 : 0.f;
+            f1 = mask_bit16(m, c, j + 1) ? f1 : 0.f;
+            f2 = mask_bit16(m, c, j + 2) ? f2 : 0.f;
+            f3 = mask_bit16(m, c, j + 3) ? f3 : 0.f;
             pk[j >> 1] = cvt_bf16x2(f0, f1);
             pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
           const uint32_t chunk_s = pro_s + (uint32_t)c * kActChunkBytes;
-#pragma unroll
-          for (int p = 0; p < 4; ++p)
-            st_shared_v4(chunk_s + rsw.piece(sub * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+          st_shared_v4(chunk_s + rsw.piece(sub * 2), pk[0], pk[1], pk[2], pk[3]);
+          st_shared_v4(chunk_s + rsw.piece(sub * 2 + 1), pk[4], pk[5], pk[6], pk[7]);
         }
         signal(kDgBarPro);
-        named_bar_sync(1, kDgEpiThreads);
-        if (et == 0) {
-          bulk_s2g(a.gstash + img_off(kGstashG9, 2, tile, a.num_tiles), s_pro, 2 * kActChunkBytes);
-          bulk_commit();
-        }
       } else {
-        const uint4 mw4 = *reinterpret_cast<const uint4*>(mask_tile + ((size_t)7 * 128 + row) * 8 + sub * 4);
-        const uint32_t mw[4] = {mw4.x, mw4.y, mw4.z, mw4.w};
+        const uint2 mw2 = __ldg(reinterpret_cast<const uint2*>(mask_tile + ((size_t)7 * 128 + row) * 8 + sub * 2));
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          uint32_t pk[16];
+          const uint32_t m = (c < 2) ? mw2.x : mw2.y;
+          uint32_t pk[8];
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 w = ld_shared_f4(wsig_s + (c * 64 + sub * 32 + j) * 4);
-            const float f0 = mask_bit(mw[c], j) ? dsig * w.x : 0.f, f1 = mask_bit(mw[c], j + 1) ? dsig * w.y : 0.f;
-            const float f2 = mask_bit(mw[c], j + 2) ? dsig * w.z : 0.f, f3 = mask_bit(mw[c], j + 3) ? dsig * w.w : 0.f;
+          for (int j = 0; j < 16; j += 4) {
+            const float4 w = ld_shared_f4(wsig_s + (c * 64 + sub * 16 + j) * 4);
+            const float f0 = mask_bit16(m, c, j) ? dsig * w.x : 0.f, f1 = mask_bit16(m, c, j + 1) ? dsig * w.y : 0.f;
+            const float f2 = mask_bit16(m, c, j + 2) ? dsig * w.z : 0.f, f3 = mask_bit16(m, c, j + 3) ? dsig * w.w : 0.f;
             pk[j >> 1] = cvt_bf16x2(f0, f1);
             pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
           const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-#pragma unroll
-          for (int p = 0; p < 4; ++p)
-            st_shared_v4(chunk_s + rsw.piece(sub * 4 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
+          acquire(c);
+          st_shared_v4(chunk_s + rsw.piece(sub * 2), pk[0], pk[1], pk[2], pk[3]);
+          st_shared_v4(chunk_s + rsw.piece(sub * 2 + 1), pk[4], pk[5], pk[6], pk[7]);
           signal(c);
-        }
-        named_bar_sync(1, kDgEpiThreads);
-        if (et == 0) {
-          bulk_s2g(a.gstash + img_off(4 * 7, 4, tile, a.num_tiles), s_act, 4 * kActChunkBytes);
-          bulk_commit();
         }
       }
       return dsig;
@@ -231,52 +254,83 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
       if (kFull) {
         dsig = dsig_next;
       } else {
-        // s_act is both the last layer's output (being stored) and this prologue's destination
-        if (et == 0) bulk_wait_read0();
-        named_bar_sync(1, kDgEpiThreads);
         dsig = prologue(tile);
       }
 #pragma unroll 1
       for (int i = 0; i < kMmaLayers; ++i, ++g) {
         const int t = (kFull ? 8 : 6) - i;  // this epilogue produces G_t
-        uint32_t mw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-        if (t < 8) {   // issued before the wait so that the load latency hides behind the MMAs
-          const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(mask_tile + ((size_t)t * 128 + row) * 8 + sub * 4));
-          mw[0] = m4.x; mw[1] = m4.y; mw[2] = m4.z; mw[3] = m4.w;
-        }
+        uint2 mw = make_uint2(0xffffffffu, 0xffffffffu);
+        if (t < 8)   // issued before the wait so that the load latency hides behind the MMAs
+          mw = __ldg(reinterpret_cast<const uint2*>(mask_tile + ((size_t)t * 128 + row) * 8 + sub * 2));
         const uint32_t b = g & 1u;
         mbar_wait(bar_acc + b, (g >> 1) & 1u);
         tc_fence_after();
-        if (et == 0) bulk_wait_read0();   // the previous image store may still be reading s_act
-        named_bar_sync(1, kDgEpiThreads);
         const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + b * 256;
-        const bool feed = t > 0;
-        uint32_t va[32], vb[32];
-        tmem_ld32(t_acc + sub * 32, va);
+        uint32_t va[16], vb[16];
+        tmem_ld16(t_acc + sub * 16, va);
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          uint32_t(&v)[32] = (c & 1) ? vb : va;
-          uint32_t(&vn)[32] = (c & 1) ? va : vb;
-          tmem_ld_wait_dep(v);
-          if (c + 1 < 4) tmem_ld32(t_acc + (c + 1) * 64 + sub * 32, vn);
-          const int c0 = c * 64 + sub * 32;
+          uint32_t(&v)[16] = (c & 1) ? vb : va;
+          uint32_t(&vn)[16] = (c & 1) ? va : vb;
+          tmem_ld_wait_dep16(v);
+          if (c + 1 < 4) tmem_ld16(t_acc + (c + 1) * 64 + sub * 16, vn);
+          const int c0 = c * 64 + sub * 16;
           const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-          if (kFull && t == 7) epi_dgrad32<true>(v, c0, mw[c], dsig, wsig_s, rsw, chunk_s, sub * 4);
-          else epi_dgrad32<false>(v, c0, mw[c], dsig, wsig_s, rsw, chunk_s, sub * 4);
-          if (feed) signal(c);
-        }
-        if (!feed) fence_async_smem();
-        named_bar_sync(1, kDgEpiThreads);
-        if (et == 0) {
-          const int slot = (t == 8) ? kGstashG8 : 4 * t;
-          bulk_s2g(a.gstash + img_off(slot, 4, tile, a.num_tiles), s_act, 4 * kActChunkBytes);
-          bulk_commit();
+          const uint32_t m = (c < 2) ? mw.x : mw.y;
+          acquire(c);
+          if (kFull && t == 7) epi_dgrad16<true>(v, c, c0, m, dsig, wsig_s, rsw, chunk_s, sub * 2);
+          else epi_dgrad16<false>(v, c, c0, m, dsig, wsig_s, rsw, chunk_s, sub * 2);
+          if (t > 0) {
+            signal(c);   // the UMMA issuer and the store warp take it from here
+          } else {       // G0: the store warp only
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_s + c);
+          }
         }
         // full mode: s_pro is free once this tile's first GEMM is done -> stage the next tile's G9 now
         if (kFull && i == 0 && next < a.num_tiles) dsig_next = prologue(next);
       }
     }
-    if (et == 0) bulk_wait_all0();
+  } else if (lane == 0) {
+    // ===================== G-image store warp =====================
+    // One thread follows the epilogue's production order: as soon as an operand image is complete (bar_a) it is
+    // bulk-copied to the G stash; once the copy has read the buffer (one copy behind, so two are in flight) the
+    // epilogue may overwrite it (bar_free).
+    uint32_t s_par = 0;
+    int pending = -1;
+    auto store = [&](int idx, bool own_bar, const uint8_t* src, uint8_t* dst, uint32_t bytes) {
+      const int pb = own_bar ? 8 + idx : idx;
+      mbar_wait(own_bar ? bar_s + idx : bar_a + idx, (s_par >> pb) & 1u);
+      s_par ^= 1u << pb;
+      bulk_s2g(dst, src, bytes);
+      bulk_commit();
+      if (pending >= 0) {
+        bulk_wait_read1();
+        mbar_arrive(bar_free + pending);
+      }
+      pending = idx;
+    };
+    auto store_act = [&](int slot, int tile) {
+      uint8_t* dst = a.gstash + img_off(slot, 4, tile, a.num_tiles);
+      for (int c = 0; c < 4; ++c)
+        store(c, slot == 0, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes, kActChunkBytes);
+    };
+    int tile = blockIdx.x;
+    if (kFull && tile < a.num_tiles)
+      store(kDgBarPro, false, s_pro, a.gstash + img_off(kGstashG9, 2, tile, a.num_tiles), 2 * kActChunkBytes);
+    for (; tile < a.num_tiles; tile += gridDim.x) {
+      const int next = tile + gridDim.x;
+      if (!kFull) store_act(4 * 7, tile);
+#pragma unroll 1
+      for (int i = 0; i < kMmaLayers; ++i) {
+        const int t = (kFull ? 8 : 6) - i;
+        store_act(t == 8 ? kGstashG8 : 4 * t, tile);
+        if (kFull && i == 0 && next < a.num_tiles)
+          store(kDgBarPro, false, s_pro, a.gstash + img_off(kGstashG9, 2, next, a.num_tiles), 2 * kActChunkBytes);
+      }
+    }
+    bulk_wait_all0();
   }
   tc_fence_before();
   __syncthreads();
@@ -289,7 +343,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
 template <bool kFull>
 static int launch_dgrad_t(const DgradArgs& a, cudaStream_t st) {
   static bool configured = false;
-  const int smem_bytes = (int)kDgSmTotal + 1024;
+  const int smem_bytes = (int)kDgSmTotal;
   if (!configured) {
     NRF_CUDA(cudaFuncSetAttribute(mlp_dgrad_kernel<kFull>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     configured = true;

@@ -257,5 +257,105 @@ __device__ __forceinline__ void epi_dgrad32(const uint32_t (&v)[32], int c0, uin
   for (int p = 0; p < 4; ++p) st_shared_v4(chunk_saddr + rs.piece(p0 + p), pk[4 * p], pk[4 * p + 1], pk[4 * p + 2], pk[4 * p + 3]);
 }
 
+// ---- 16-column granularity (16 epilogue warps: 4 per TMEM lane quarter, each owning columns
+// [c*64 + sub*16, +16) of every 64-column chunk c) -------------------------------------------------------
+// Sign masks: a thread pushes its 16 columns of chunks 0,1 into one word and of chunks 2,3 into a second one;
+// column j of chunk c is bit 31 - ((c & 1) * 16 + j) of word c >> 1 (after inversion: 1 = positive).
+__device__ __forceinline__ bool mask_bit16(uint32_t pos_word, int c, int j) { return (pos_word >> (31 - ((c & 1) * 16 + j))) & 1u; }
+
+template <bool kRelu, bool kMask, bool kDot>
+__device__ __forceinline__ void epi_fwd16(const uint32_t (&v)[16], int c0, uint32_t bias_saddr, uint32_t wdot_saddr,
+                                          const RowSwz& rs, uint32_t chunk_saddr, int p0, uint32_t& sign_reg, float& dot) {
+  uint32_t pk[8];
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    const float4 b = ld_shared_f4(bias_saddr + (c0 + j) * 4);
+    const float x0 = __uint_as_float(v[j]) + b.x, x1 = __uint_as_float(v[j + 1]) + b.y;
+    const float x2 = __uint_as_float(v[j + 2]) + b.z, x3 = __uint_as_float(v[j + 3]) + b.w;
+    if (kMask) {
+      sign_reg = push_sign(sign_reg, x0); sign_reg = push_sign(sign_reg, x1);
+      sign_reg = push_sign(sign_reg, x2); sign_reg = push_sign(sign_reg, x3);
+    }
+    if (kDot) {
+      const float4 w = ld_shared_f4(wdot_saddr + (c0 + j) * 4);
+      dot += fmaxf(x0, 0.f) * w.x + fmaxf(x1, 0.f) * w.y + fmaxf(x2, 0.f) * w.z + fmaxf(x3, 0.f) * w.w;
+    }
+    pk[j >> 1] = kRelu ? cvt_relu_bf16x2(x0, x1) : cvt_bf16x2(x0, x1);
+    pk[(j >> 1) + 1] = kRelu ? cvt_relu_bf16x2(x2, x3) : cvt_bf16x2(x2, x3);
+  }
+  st_shared_v4(chunk_saddr + rs.piece(p0), pk[0], pk[1], pk[2], pk[3]);
+  st_shared_v4(chunk_saddr + rs.piece(p0 + 1), pk[4], pk[5], pk[6], pk[7]);
+}
+
+template <bool kAddSig>
+__device__ __forceinline__ void epi_dgrad16(const uint32_t (&v)[16], int c, int c0, uint32_t pos_word, float dsig,
+                                            uint32_t wsig_saddr, const RowSwz& rs, uint32_t chunk_saddr, int p0) {
+  uint32_t pk[8];
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    float f0 = __uint_as_float(v[j]), f1 = __uint_as_float(v[j + 1]), f2 = __uint_as_float(v[j + 2]),
+          f3 = __uint_as_float(v[j + 3]);
+    if (kAddSig) {
+      const float4 w = ld_shared_f4(wsig_saddr + (c0 + j) * 4);
+      f0 = fmaf(dsig, w.x, f0); f1 = fmaf(dsig, w.y, f1); f2 = fmaf(dsig, w.z, f2); f3 = fmaf(dsig, w.w, f3);
+    }
+    f0 = mask_bit16(pos_word, c, j) ? f0 : 0.f;
+    f1 = mask_bit16(pos_word, c, j + 1) ? f1 : 0.f;
+    f2 = mask_bit16(pos_word, c, j + 2) ? f2 : 0.f;
+    f3 = mask_bit16(pos_word, c, j + 3) ? f3 : 0.f;
+    pk[j >> 1] = cvt_bf16x2(f0, f1);
+    pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
+  }
+  st_shared_v4(chunk_saddr + rs.piece(p0), pk[0], pk[1], pk[2], pk[3]);
+  st_shared_v4(chunk_saddr + rs.piece(p0 + 1), pk[4], pk[5], pk[6], pk[7]);
+}
+
+// 16 consecutive columns [kPart*16, +16) of the encoded row as 8 bf16x2 words (see encode_half)
+template <int kPart, int kL>
+__device__ __forceinline__ void encode_cols16(const float (&p)[3], uint32_t (&w)[8]) {
+  constexpr int kFirst = kPart * 16, kLast = kFirst + 15;
+  constexpr int kK0 = kFirst < 3 ? 0 : (kFirst - 3) / 6;
+  constexpr int kKl = kLast < 3 ? 0 : (kLast - 3) / 6;
+  constexpr int kK1 = kKl < kL - 1 ? kKl : kL - 1;
+  constexpr bool kAny = kLast >= 3 && kK1 >= kK0 && kFirst < 3 + 6 * kL;
+  constexpr int kNK = kAny ? kK1 - kK0 + 1 : 0;
+  float sn[kNK > 0 ? kNK : 1][3], cs[kNK > 0 ? kNK : 1][3];
+  if (kNK > 0) {
+    const TurnArg ta[3] = {TurnArg(p[0]), TurnArg(p[1]), TurnArg(p[2])};
+#pragma unroll
+    for (int k = 0; k < kNK; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) ta[c].sincos_pow2(kK0 + k, &sn[k][c], &cs[k][c]);
+  }
+  float v[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int col = kFirst + i;
+    float x = 0.f;
+    if (col < 3) {
+      x = p[col];
+    } else if (col < 3 + 6 * kL) {
+      const int e = col - 3, k = e / 6, f = (e % 6) / 3, c = e % 3;
+      x = f ? cs[k - kK0][c] : sn[k - kK0][c];
+    }
+    v[i] = x;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) w[i] = cvt_bf16x2(v[2 * i], v[2 * i + 1]);
+}
+
+// thread (row, part 0..3) writes 16 columns of the encoded row into the chunk at tile_saddr
+template <int kL>
+__device__ __forceinline__ void encode_store16(int part, const float (&p)[3], uint32_t tile_saddr, int row) {
+  uint32_t w[8];
+  if (part == 0) encode_cols16<0, kL>(p, w);
+  else if (part == 1) encode_cols16<1, kL>(p, w);
+  else if (part == 2) encode_cols16<2, kL>(p, w);
+  else encode_cols16<3, kL>(p, w);
+  const RowSwz rs(row);
+  st_shared_v4(tile_saddr + rs.piece(part * 2), w[0], w[1], w[2], w[3]);
+  st_shared_v4(tile_saddr + rs.piece(part * 2 + 1), w[4], w[5], w[6], w[7]);
+}
+
 }  // namespace tc
 }  // namespace nrf
