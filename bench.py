@@ -24,6 +24,30 @@ FLOP_PER_SAMPLE_FWDBWD = 3489024
 FLOP_PER_SAMPLE_FWD = 1186816
 FLOP_PER_RAY_TRAIN = FLOP_PER_SAMPLE_FWDBWD * (NC + NC + NF)
 
+# The tensor-core MLP kernels of one training step (ids = NRF_K_* of include/nerf_b200.h), with their ALGORITHMIC
+# work per sample row: FLOPs of the GEMM chain, and HBM bytes that have to move once (operand-image
+# stash written / read back, sign masks, per-sample inputs / outputs; the L2-resident weights are not counted).
+#   stash image = 128 B per row and 64-column chunk; full model 40 chunks (34 sigma-only), G images 38 (32)
+# In a training step both passes evaluate the full model (the coarse rgb enters the loss, rendering.py:236-247), so
+# each "full" kernel launches twice per step: 4096 x 64 rows (coarse) and 4096 x 128 rows (fine).
+KERNELS = {
+    2: ("mlp_fwd_kernel<sigma,train>", 982528, 34 * 128 + 256 + 4 + 4),
+    3: ("mlp_fwd_kernel<full,train>", 1186816, 40 * 128 + 272 + 16 + 4),
+    4: ("mlp_dgrad_kernel<sigma>", 7 * 131072, 32 * 128 + 256 + 4),
+    5: ("mlp_dgrad_kernel<full>", 65536 + 8 * 131072, 38 * 128 + 272 + 16 + 12 + 16),
+    6: ("mlp_wgrad_kernel (sigma)", 982528, (33 + 32) * 128 + 4),
+    7: ("mlp_wgrad_kernel (full)", 1186816, (40 + 38) * 128 + 4 + 16),
+}
+
+
+def ncu_traffic():
+    """DRAM bytes per launch of each kernel from the committed `ncu --set full` capture (profiles/), or {}."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")) as f:
+            return {int(k): v for k, v in json.load(f)["dram_bytes_per_launch"].items()}
+    except Exception:
+        return {}
+
 
 def load_peaks():
     try:
@@ -191,12 +215,14 @@ def run_gpu(args):
     launches0 = lib.nrf_launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     sync_all()
+    lib.nrf_prof_enable(1)          # CUDA-event pair around every tensor-core MLP launch, on the launching stream
     for i in range(K):
         flush.zero_()
         ev[i][0].record()
         step(rays_dev, rgbs_dev)
         ev[i][1].record()
     sync_all()
+    lib.nrf_prof_enable(0)
     launches = (lib.nrf_launch_count() - launches0) / K
     ms = sum(a.elapsed_time(b) for a, b in ev) / K
     # ---- end to end: pinned host -> device copies and the loss read-back inside the timed region ------
@@ -222,9 +248,43 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = float(t[0]), float(t[1])
 
-    # ---- roofline of the dominant kernel: the tensor-core MLP forward on the fine pass (4096 x 128 rows) ---
+    # ---- roofline: every tensor-core MLP kernel of the step, timed live over the timed region above ------------
     roof = None
     if args.precision == "bf16":
+        import ctypes
+        traffic = ncu_traffic()
+        table = []
+        for kid, (name, flop_row, byte_row) in KERNELS.items():
+            tot, n, nrows = ctypes.c_double(0.0), ctypes.c_int64(0), ctypes.c_int64(0)
+            _lib.check(lib.nrf_prof_read(kid, ctypes.byref(tot), ctypes.byref(n), ctypes.byref(nrows)), "nrf_prof_read")
+            if n.value == 0:
+                continue
+            rows = nrows.value / n.value          # average over the launches (coarse and fine pass)
+            k_ms = tot.value / n.value
+            tf = rows * flop_row / (k_ms * 1e-3) / 1e12
+            gbs = rows * byte_row / (k_ms * 1e-3) / 1e9
+            f_t, f_h = tf / peaks["bf16_tflops"], gbs / peaks["hbm_gbs"]
+            table.append({"id": kid, "kernel": f"nrf::tc::{name}", "rows_per_launch": rows, "launches_per_step": n.value / K,
+                          "ms_per_launch": k_ms, "ms_per_step": tot.value / K, "flop_per_row": flop_row,
+                          "hbm_bytes_per_row": byte_row, "tflops": tf, "tensor_frac": f_t,
+                          "gbs": gbs, "hbm_frac": f_h, "bound": "hbm" if f_h >= f_t else "tensor",
+                          "traffic": traffic.get(kid)})
+        if table:
+            dom = max(table, key=lambda r: r["ms_per_step"])
+            hbm = dom["bound"] == "hbm"
+            roof = {"bound": dom["bound"],
+                    "kernel": f"{dom['kernel']}, {dom['launches_per_step']:.0f} launches per step, "
+                              f"{dom['rows_per_launch']:.0f} sample rows per launch on average",
+                    "achieved": dom["gbs"] if hbm else dom["tflops"],
+                    "peak": peaks["hbm_gbs"] if hbm else peaks["bf16_tflops"],
+                    "unit": "GB/s" if hbm else "TFLOP/s",
+                    "frac": dom["hbm_frac"] if hbm else dom["tensor_frac"],
+                    "peak_source": f"{peaks['src']} (" + ("copy bandwidth" if hbm else "sustained: kernel timed inside the step") + ")",
+                    "ms_per_launch": dom["ms_per_launch"], "share_of_step": dom["ms_per_step"] / ms,
+                    "traffic": dom["traffic"],
+                    "mlp_kernels_share_of_step": sum(r["ms_per_step"] for r in table) / ms,
+                    "kernels": table}
+        # the same forward kernel without the stash (inference), timed alone: how close the GEMM chain itself gets
         z = torch.sort(torch.rand(B, NC + NF, device=dev) * 4 + 2, -1)[0]
         params = [p.detach() for p in models[1].ordered_parameters()]
         packed = models[1].packed_weights()
@@ -239,11 +299,11 @@ def run_gpu(args):
         e1.record()
         torch.cuda.synchronize()
         k_ms = e0.elapsed_time(e1) / reps
-        flops = B * (NC + NF) * FLOP_PER_SAMPLE_FWD
-        ach = flops / (k_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "kernel": "nrf::tc::mlp_fwd_kernel<full,inference> (4096 rays x 128 samples)",
-                "achieved": ach, "peak": peaks["bf16_burst"], "unit": "TFLOP/s", "frac": ach / peaks["bf16_burst"],
-                "peak_source": f"{peaks['src']} (burst: kernel timed alone)", "ms_per_launch": k_ms, "traffic": None}
+        ach = B * (NC + NF) * FLOP_PER_SAMPLE_FWD / (k_ms * 1e-3) / 1e12
+        if roof is not None:
+            roof["inference_forward"] = {"kernel": "nrf::tc::mlp_fwd_kernel<full,inference> (4096 rays x 128 samples), timed alone",
+                                         "ms_per_launch": k_ms, "tflops": ach, "peak": peaks["bf16_burst"],
+                                         "frac": ach / peaks["bf16_burst"]}
 
     if rank == 0:
         rays_per_s = world * B / (ms * 1e-3)

@@ -39,6 +39,22 @@ int nrf_check_device(void);
 /* Number of CUDA kernels this library has launched in the calling process so far. */
 uint64_t nrf_launch_count(void);
 
+/* Per-kernel device timing of the tensor-core MLP kernels (measurement aid; bench.py's roofline).  While enabled,
+ * every launch is bracketed by a CUDA event pair on its own stream.  nrf_prof_enable(1) discards earlier records and
+ * starts a session, nrf_prof_enable(0) stops recording (records stay readable); nrf_prof_read waits for the
+ * recorded launches of one kernel and returns their summed duration, their count and the sample rows they processed. */
+#define NRF_K_FWD_SIGMA_INFER 0
+#define NRF_K_FWD_FULL_INFER 1
+#define NRF_K_FWD_SIGMA_TRAIN 2
+#define NRF_K_FWD_FULL_TRAIN 3
+#define NRF_K_DGRAD_SIGMA 4
+#define NRF_K_DGRAD_FULL 5
+#define NRF_K_WGRAD_SIGMA 6
+#define NRF_K_WGRAD_FULL 7
+#define NRF_K_COUNT 8
+int nrf_prof_enable(int on);
+int nrf_prof_read(int kernel_id, double* total_ms, int64_t* launches, int64_t* rows);
+
 /* a4  stratified depth sampling — models/rendering.py:216-232
  * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);
  * u (N,n_samples) uniform [0,1) or NULL (required iff perturb > 0); z_out (N,n_samples). */

@@ -33,6 +33,8 @@ SIGNATURES = {
     "nrf_last_error": (c_char_p, []),
     "nrf_check_device": (I, []),
     "nrf_launch_count": (ctypes.c_uint64, []),
+    "nrf_prof_enable": (I, [I]),
+    "nrf_prof_read": (I, [I, P, P, P]),
     "nrf_sample_coarse": (I, [P, P, L, I, I, F, P, P, P]),
     "nrf_embed_fwd": (I, [P, L, I, P, I, P, P]),
     "nrf_embed_bwd": (I, [P, P, L, I, P, I, P, P]),

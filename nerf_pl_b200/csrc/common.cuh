@@ -33,6 +33,17 @@ extern unsigned long long g_launches;  // kernels launched by this library (stat
     NRF_CUDA(cudaGetLastError()); \
   } while (0)
 
+// Optional per-kernel device timing (nrf_prof_enable / nrf_prof_read, error.cu): an event pair is recorded around
+// the launch on the launching stream; a no-op unless enabled.
+extern bool g_prof_on;
+void prof_record(int kernel_id, cudaStream_t st, bool begin, int64_t rows);
+struct ProfScope {
+  int id;
+  cudaStream_t st;
+  ProfScope(int kernel_id, cudaStream_t s, int64_t rows) : id(kernel_id), st(s) { if (g_prof_on) prof_record(id, st, true, rows); }
+  ~ProfScope() { if (g_prof_on) prof_record(id, st, false, 0); }
+};
+
 static inline cudaStream_t as_stream(nrf_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 constexpr int kNumSMs = 148;  // B200

@@ -479,6 +479,7 @@ static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
   NRF_CUDA(cudaGetDevice(&dev));
   NRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int grid = a.num_tiles < sms ? a.num_tiles : sms;
+  ProfScope prof((kTrain ? NRF_K_FWD_SIGMA_TRAIN : NRF_K_FWD_SIGMA_INFER) + (kFull ? 1 : 0), st, a.n_rows);
   mlp_fwd_kernel<kFull, kTrain><<<grid, kTrain ? kThreadsTrain : kThreadsInfer, smem_bytes, st>>>(a);
   NRF_LAUNCH_CHECK();
   return NRF_OK;

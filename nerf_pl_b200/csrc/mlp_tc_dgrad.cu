@@ -351,6 +351,7 @@ static int launch_dgrad_t(const DgradArgs& a, cudaStream_t st) {
   int dev = 0, sms = kNumSMs;
   NRF_CUDA(cudaGetDevice(&dev));
   NRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  ProfScope prof(kFull ? NRF_K_DGRAD_FULL : NRF_K_DGRAD_SIGMA, st, a.n_rows);
   mlp_dgrad_kernel<kFull><<<a.num_tiles < sms ? a.num_tiles : sms, kDgThreads, smem_bytes, st>>>(a);
   NRF_LAUNCH_CHECK();
   return NRF_OK;

@@ -451,6 +451,7 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
     configured = true;
   }
   NRF_CUDA(cudaMemsetAsync(unit_counter, 0, sizeof(int), st));
+  ProfScope prof(full ? NRF_K_WGRAD_FULL : NRF_K_WGRAD_SIGMA, st, n_rows);
   mlp_wgrad_kernel<<<std::min(a.total_units, sms), kWgThreads, smem_bytes, st>>>(a);
   NRF_LAUNCH_CHECK();
   return NRF_OK;

@@ -15,7 +15,11 @@ def shard_bounds(n_items: int, rank: int, world: int):
 
 class GradBucket:
     """One flat fp32 buffer aliasing every parameter's .grad, so the gradient all-reduce is a single
-    collective launch (latency-bound at 4.77 MB; NVSwitch makes it ~tens of microseconds)."""
+    collective launch (latency-bound at 4.77 MB; NVSwitch makes it ~tens of microseconds).
+
+    NeRF modules are also told where their gradients live (`_nrf_grad_sinks`): the fused render pass then lets its
+    backward kernels add into the bucket directly instead of handing zero-initialised temporaries to autograd
+    (mlp.backward_rays), as long as the parameters' .grad still are the bucket's views."""
 
     def __init__(self, modules):
         self.params = [p for m in modules for p in m.parameters() if p.requires_grad]
@@ -25,6 +29,9 @@ class GradBucket:
         for p in self.params:
             p.grad = self.flat[off:off + p.numel()].view_as(p)
             off += p.numel()
+        for m in modules:
+            if hasattr(m, "ordered_parameters") and all(p.requires_grad for p in m.parameters()):
+                m.__dict__["_nrf_grad_sinks"] = [p.grad for p in m.ordered_parameters()]
 
     def zero(self):
         self.flat.zero_()

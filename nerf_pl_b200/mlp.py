@@ -57,12 +57,19 @@ def forward_rays(spec, params, rays, z, sigma_only, need_grad, precision, xyz_fr
     return sigma, rgb, ("fp32", ws if need_grad else None)
 
 
-def backward_rays(spec, params, rays, z, sigma_only, saved, d_sigma, d_rgb, rgb):
+def backward_rays(spec, params, rays, z, sigma_only, saved, d_sigma, d_rgb, rgb, grad_sinks=None):
+    """Parameter gradients.  The kernels ACCUMULATE (atomic adds from many CTAs), so by default they run on
+    zero-filled tensors that are returned to autograd.  With `grad_sinks` (dist.GradBucket: one fp32 tensor per
+    parameter, aliasing its .grad) they add straight into the sinks and a list of None is returned: no 24 fills and
+    no 24 AccumulateGrad additions per pass."""
     lib = _lib.load()
     N, S = z.shape
-    grads = [torch.zeros_like(p) for p in params]
+    if grad_sinks is not None:
+        grads, ret = grad_sinks, [None] * len(params)
+    else:
+        grads = ret = [torch.zeros_like(p) for p in params]
     if N == 0:
-        return grads
+        return ret
     gs = spec.grads_struct(grads)
     if saved[0] == "tc_recompute":
         # interim: parameter gradients of the bf16 forward are evaluated by the fp32 kernels at the same
@@ -87,7 +94,19 @@ def backward_rays(spec, params, rays, z, sigma_only, saved, d_sigma, d_rgb, rgb)
         ps = spec.params_struct(params)
         _lib.call("nrf_mlp_fp32_bwd", byref(ps), byref(gs), None, N * S, N, S, int(sigma_only), _p(d_sigma),
                   _p(d_rgb), _p(rgb), _p(ws), ws.numel(), _stream())
-    return grads
+    return ret
+
+
+def _live_sinks(cfg, params):
+    """cfg.grad_sinks if they still alias the parameters' .grad (the user may have dropped or replaced them)."""
+    sinks = getattr(cfg, "grad_sinks", None)
+    if sinks is None or len(sinks) != len(params):
+        return None
+    for p, s in zip(params, sinks):
+        g = p.grad
+        if g is None or g.data_ptr() != s.data_ptr() or g.shape != s.shape:
+            return None
+    return sinks
 
 
 class RenderPass(torch.autograd.Function):
@@ -119,7 +138,8 @@ class RenderPass(torch.autograd.Function):
         rgb_s = rgb_s if rgb_s.numel() else None
         d_sigma, d_rgb = ops.composite_bwd(sigma, rgb_s, z, rays, noise, cfg.noise_std, cfg.white_back,
                                            g_rgb if rgb_s is not None else None, g_depth, g_opacity, g_disp)
-        grads = backward_rays(cfg.spec, params, rays, z, cfg.sigma_only, ctx.saved, d_sigma, d_rgb, rgb_s)
+        grads = backward_rays(cfg.spec, params, rays, z, cfg.sigma_only, ctx.saved, d_sigma, d_rgb, rgb_s,
+                              _live_sinks(cfg, params))
         ctx.saved = None
         return (None, None, None, None, *grads)
 

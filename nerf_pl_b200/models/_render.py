@@ -35,7 +35,8 @@ def _model_cfg(model, embeddings, sigma_only, white_back, noise_std):
     packed = model.packed_weights() if (precision == "bf16" and spec.tc_capable) else None
     return SimpleNamespace(spec=spec, sigma_only=bool(sigma_only), white_back=bool(white_back),
                            noise_std=float(noise_std), precision=precision, packed=packed,
-                           xyz_freqs=int(ex.N_freqs), dir_freqs=int(ed.N_freqs))
+                           xyz_freqs=int(ex.N_freqs), dir_freqs=int(ed.N_freqs),
+                           grad_sinks=model.__dict__.get("_nrf_grad_sinks"))
 
 
 def sample_pdf(rays, weights, N_importance, det=False, eps=1e-5, _u=None, _jitter=None):

@@ -286,3 +286,58 @@ def test_tc_backward_vs_bf16_emulation(dev, sigma_only, N, S):
     print("   vs emulation: " + " ".join(f"{short(k)}={v:.1e}" for k, v in errs.items()))
     print("   vs fp32 kernels (informational): " + " ".join(f"{short(k)}={v:.1e}" for k, v in errs32.items()))
     assert worst < 2e-2, errs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_grad_bucket_direct_sinks_match_autograd(dev, precision):
+    """dist.GradBucket lets the backward kernels add straight into the flat gradient buffer (mlp.backward_rays,
+    grad_sinks); the result must equal the gradients autograd accumulates from zero-filled temporaries, up to the
+    order of the fp32 atomic additions, over TWO backward passes (accumulation) and after the user replaces a .grad
+    (the sinks then fall back to autograd)."""
+    import nerf_pl_b200
+    from nerf_pl_b200.dist import GradBucket
+    from nerf_pl_b200.models.nerf import Embedding, NeRF
+    from nerf_pl_b200.models.rendering import render_rays
+    nerf_pl_b200.set_mlp_precision(precision)
+    try:
+        emb = [Embedding(3, 10), Embedding(3, 4)]
+        rays = O.blender_rays(192, seed=3).to(dev)
+        tgt = torch.rand(192, 3, generator=torch.Generator().manual_seed(4)).to(dev)
+
+        def make():
+            ms = []
+            for s in (0, 1):
+                m = NeRF().to(dev)
+                m.load_state_dict(O.init_mlp_params(generator=torch.Generator().manual_seed(s)))
+                ms.append(m)
+            return ms
+
+        def run(ms, passes):
+            for _ in range(passes):
+                torch.manual_seed(11)
+                out = render_rays(ms, emb, rays, 64, False, 1.0, 1.0, 64, 1024 * 32, True)
+                (((out["rgb_coarse"] - tgt) ** 2).mean() + ((out["rgb_fine"] - tgt) ** 2).mean()).backward()
+
+        plain, sunk = make(), make()
+        bucket = GradBucket(sunk)
+        assert all("_nrf_grad_sinks" in m.__dict__ for m in sunk)
+        run(plain, 2)
+        run(sunk, 2)
+        tol = 1e-4 if precision == "fp32" else 2e-3   # bf16: the stash is identical, only the atomic order differs
+        for mp, ms_ in zip(plain, sunk):
+            for (n, a), (_, b) in zip(mp.named_parameters(), ms_.named_parameters()):
+                assert b.grad.data_ptr() >= bucket.flat.data_ptr()
+                ref = a.grad
+                rel = (b.grad - ref).norm().item() / (ref.norm().item() + 1e-20)
+                assert rel < tol, f"{n}: {rel:.2e}"
+        # a replaced .grad disables the sinks for that model: autograd accumulates into the new tensor
+        first = next(sunk[1].parameters())
+        first.grad = torch.zeros_like(first)
+        flat_before = bucket.flat.clone()
+        run(sunk, 1)
+        assert first.grad.abs().sum().item() > 0
+        off = sum(p.numel() for p in sunk[0].parameters())
+        assert torch.equal(bucket.flat[off:off + first.numel()], flat_before[off:off + first.numel()])
+    finally:
+        nerf_pl_b200.set_mlp_precision("bf16")
