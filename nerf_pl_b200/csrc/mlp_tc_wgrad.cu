@@ -5,11 +5,13 @@
 // reduction dimension K is the ROW index, so no transpose is ever materialised:
 //   D[n_out (M=128 half), k_in (N<=256)] += A(MN-major, M = 128 cols of G) * B(MN-major, N = cols of X),
 //   K = 16 rows per tcgen05.mma.
-// Work is cut into units = (weight matrix, slab of tiles); persistent CTAs pull units from a global
-// atomic counter (units of different matrices stream different byte counts, so static assignment
-// leaves SMs idle).  The full fp32 dW block (2 halves x 256 columns = all 512 TMEM columns) stays in
-// TMEM across a unit and is flushed once with fp32 reductions (red.global.add, vectorised when the
-// destination row pitch allows).  Stages are 32-row slices (4 KB per chunk) streamed through a
+// Work = jobs (one weight matrix each) cut into granules of a few tiles that persistent CTAs claim through
+// per-job atomic counters.  A CTA stays on one job while that job has granules left: the full fp32 dW block
+// (2 halves x 256 columns = all 512 TMEM columns) keeps accumulating in TMEM and is flushed with fp32
+// reductions (red.global.add, vectorised when the destination row pitch allows) only when the CTA moves to
+// another job -- the flush of 64 K atomics was measured at ~0.3 ms per step when it ran 8 times per SM.
+// CTAs start spread over the jobs in proportion to the jobs' byte counts and help out elsewhere once their job
+// is exhausted, so the tail is one granule.  Stages are 32-row slices (4 KB per chunk) streamed through a
 // 6-deep ring; the copies of one stage are issued by different lanes of the producer warp (a single
 // thread issuing them serially was the bottleneck of the first version: profiles/r01_*baseline*).
 // Bias gradients (column sums of G) and the tiny sigma / rgb head gradients run on the otherwise
@@ -47,19 +49,20 @@ struct WgradJob {
   float* dW; int ld;           // destination (row = n_out)
   float* db;                   // bias gradient = column sums of G, or null
   int side, side_off;          // 0: none; 1: sigma head, h7 = X slices side_off..+3; 2: rgb head, dmid = X slices side_off..+1
-  int first_unit, n_units, tiles_per_unit;
+  int n_gran, tiles_per_gran;  // work granules of this job (claimed dynamically through counters[job])
+  int first_cta;               // CTAs [first_cta, next job's first_cta) start on this job
 };
 
 struct WgradArgs {
   WgradJob jobs[kWgMaxJobs];
-  int n_jobs, total_units, num_tiles;
+  int n_jobs, num_tiles;
   int64_t n_rows;
   const uint8_t* xstash;
   const uint8_t* gstash;
   const float* d_sigma;        // (rows)
   const float* dpre;           // (tiles*128, 4)
   float* dW_sigma; float* db_sigma; float* dW_rgb; float* db_rgb;
-  int* unit_counter;           // zeroed before launch
+  int* counters;               // [n_jobs] next granule of each job, zeroed before launch
   int dbg_flags;               // experiments only (NRF_DBG_FLAGS): 1 = skip side work, 2 = skip MMAs
 };
 
@@ -100,17 +103,115 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
-  uint32_t it = 0;  // stage counter (same sequence in all roles)
+  // Work distribution: a job (one layer's weight gradient) is cut into granules of a few tiles, claimed through a
+  // per-job counter.  A CTA stays on ONE job for as long as that job has granules left, so its TMEM accumulators keep
+  // summing and are flushed (64 K atomic adds) only when it moves on to another job; CTAs start spread over the jobs
+  // in proportion to the jobs' cost and help out elsewhere (cyclic scan) once their own job is exhausted.
+  uint32_t it = 0;     // stage counter (same sequence in all roles)
+  uint32_t grp = 0;    // accumulator groups flushed so far (UMMA issuer and side warps count alike)
+  int prev_job = -1;   // job of the previous unit
+  int sched_job = 0;   // scheduler: job this CTA currently draws from
+  if (warp == 0) {
+    while (sched_job + 1 < a.n_jobs && (int)blockIdx.x >= a.jobs[sched_job + 1].first_cta) ++sched_job;
+  }
+  // side-warp register accumulators (column sums of G; head gradients); live across the units of one job
+  float bs[8], hs[8], hg[8], hbv[8], hb0 = 0.f, hb1 = 0.f, hb2 = 0.f;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { bs[e] = 0.f; hs[e] = 0.f; hg[e] = 0.f; hbv[e] = 0.f; }
+  bool fresh = true;   // UMMA issuer: the next stage starts a new accumulator group
+
+  // side warps: end-of-group reduction of the register accumulators + accumulator flush of job `pj`
+  auto flush_group = [&](const WgradJob& pj) {
+    const int t = threadIdx.x - 64;
+    const int cb = t & 7, rql = (t >> 3) & 3, sw = t >> 5;
+    const int k4 = sw & 3, k2 = sw & 1;
+    const int a_chunks = pj.a_chunks;
+    const bool do_bias = pj.db != nullptr && !(a.dbg_flags & 1);
+    const int side = (a.dbg_flags & 1) ? 0 : pj.side;
+    // reduce over the four row groups that live in one warp (lane bits 3, 4), then one atomic per column and warp
+    auto warp_rows_sum = [&](float v) {
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      return v;
+    };
+    if (do_bias) {   // warp-uniform (k4 depends on the warp only)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float v = warp_rows_sum(bs[e]);
+        if (rql == 0 && k4 < a_chunks) atomicAdd(pj.db + k4 * 64 + cb * 8 + e, v);
+      }
+    }
+    if (side == 1) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float v = warp_rows_sum(hs[e]);
+        if (rql == 0) atomicAdd(a.dW_sigma + k4 * 64 + cb * 8 + e, v);
+      }
+      const float vb = warp_rows_sum(hb0);
+      if (k4 == 0 && lane == 0) atomicAdd(a.db_sigma, vb);   // cb = 0 lanes of slice-0 warps cover every row once
+    } else if (side == 2) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float v0 = warp_rows_sum(hs[e]), v1 = warp_rows_sum(hg[e]), v2 = warp_rows_sum(hbv[e]);
+        if (rql == 0) {
+          atomicAdd(a.dW_rgb + k2 * 64 + cb * 8 + e, v0);
+          atomicAdd(a.dW_rgb + 128 + k2 * 64 + cb * 8 + e, v1);
+          atomicAdd(a.dW_rgb + 256 + k2 * 64 + cb * 8 + e, v2);
+        }
+      }
+      const float w0 = warp_rows_sum(hb0), w1 = warp_rows_sum(hb1), w2 = warp_rows_sum(hb2);
+      if (k2 == 0 && lane == 0) { atomicAdd(a.db_rgb, w0); atomicAdd(a.db_rgb + 1, w1); atomicAdd(a.db_rgb + 2, w2); }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { bs[e] = 0.f; hs[e] = 0.f; hg[e] = 0.f; hbv[e] = 0.f; }
+    hb0 = hb1 = hb2 = 0.f;
+    // accumulator flush: thread = TMEM lane (n_out within the half); the two warp groups split the column blocks
+    mbar_wait(bar_acc, grp & 1);
+    tc_fence_after();
+    const int q = warp & 3, wg = (warp - 2) >> 2;
+    const int halves = (a.dbg_flags & 64) ? 0 : a_chunks >> 1;
+    const int nblk = pj.b_mma * 2;  // 32-column blocks
+    const bool vec_ok = (pj.ld & 3) == 0 && (reinterpret_cast<uintptr_t>(pj.dW) & 15) == 0;
+    for (int hh = 0; hh < halves; ++hh) {
+      float* drow = pj.dW + (size_t)(hh * 128 + q * 32 + lane) * pj.ld;
+      for (int blk = wg; blk < nblk; blk += 2) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + hh * 256 + blk * 32, v);
+        tmem_ld_wait();
+        const int ch = blk >> 1, cbase = (blk & 1) * 32;
+        const int valid = pj.b_valid[ch] - cbase;
+        float* d = drow + ch * 64 + cbase;
+        if (vec_ok && valid >= 32) {
+#pragma unroll
+          for (int c = 0; c < 32; c += 4)
+            red_add_v4(d + c, __uint_as_float(v[c]), __uint_as_float(v[c + 1]), __uint_as_float(v[c + 2]),
+                       __uint_as_float(v[c + 3]));
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (c < valid) atomicAdd(d + c, __uint_as_float(v[c]));
+        }
+      }
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_drained);
+  };
+
   for (uint32_t uq = 0;; ++uq) {
     const uint32_t us = uq & 1, uph = (uq >> 1) & 1;
-    int unit;
+    int unit;   // (job << 20) | granule, or -1: no work left
     if (warp == 0) {
-      // ---------------- scheduler: claim the next unit and publish it ----------------
+      // ---------------- scheduler: claim the next granule and publish it ----------------
       unit = 0;
       if (lane == 0) {
         mbar_wait(bar_uq_empty + us, uph ^ 1);
-        unit = atomicAdd(a.unit_counter, 1);
-        if (unit >= a.total_units) unit = -1;
+        unit = -1;
+        for (int tries = 0; tries < a.n_jobs; ++tries) {
+          const int g = atomicAdd(a.counters + sched_job, 1);
+          if (g < a.jobs[sched_job].n_gran) { unit = (sched_job << 20) | g; break; }
+          if (++sched_job == a.n_jobs) sched_job = 0;
+        }
         s_unit[us] = unit;
         mbar_arrive(bar_uq_full + us);
       }
@@ -122,13 +223,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       if (lane == 0) mbar_arrive(bar_uq_empty + us);
     }
     if (unit < 0) break;
-    int j = 0;
-    while (j + 1 < a.n_jobs && unit >= a.jobs[j + 1].first_unit) ++j;
+    const int j = unit >> 20;
     const WgradJob& job = a.jobs[j];
-    const int t0 = (unit - job.first_unit) * job.tiles_per_unit;
-    const int t1 = min(a.num_tiles, t0 + job.tiles_per_unit);
+    const int t0 = (unit & 0xfffff) * job.tiles_per_gran;
+    const int t1 = min(a.num_tiles, t0 + job.tiles_per_gran);
     const int n_stage = (t1 - t0) * 4;
     const int a_chunks = job.a_chunks, b_n = job.b_n;
+    const bool new_job = j != prev_job;
 
     if (warp == 0) {
       // ---------------- producer: lane c copies slice c of every stage ----------------
@@ -162,9 +263,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
     } else if (warp == 1) {
       // ---------------- UMMA issuer ----------------
       if (lane == 0) {
-        if (uq > 0) {  // previous unit's accumulators must be drained before they are overwritten
-          mbar_wait(bar_drained, (uq - 1) & 1);
-          tc_fence_after();
+        if (new_job) {
+          if (prev_job >= 0) {   // the previous job's accumulators are complete: hand them over and wait for the flush
+            umma_commit(bar_acc);
+            mbar_wait(bar_drained, grp & 1);
+            tc_fence_after();
+          }
+          fresh = true;
         }
         const int halves = (a.dbg_flags & 2) ? 0 : a_chunks >> 1;
         const int n_main = job.b_mma > 4 ? 4 : job.b_mma;
@@ -184,7 +289,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
 #pragma unroll
             for (int ks = 0; ks < 2; ++ks) {
               const uint64_t ad = make_desc_sw128(base + hh * 2 * kWgSlice + ks * 2048, kWgSlice, 1024);
-              const uint32_t acc = (s | ks) != 0;
+              const uint32_t acc = !(fresh && ks == 0);
               umma_ss(tmem_base + hh * 256, ad, make_desc_sw128(base + kWgASlots * kWgSlice + ks * 2048, kWgSlice, 1024),
                       idesc_main, acc);
               if (tail)
@@ -193,8 +298,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
             }
           }
           umma_commit(bar_empty + stage);
+          fresh = false;
         }
-        umma_commit(bar_acc);
       } else {
         it += n_stage;
       }
@@ -204,6 +309,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       // (physical piece = cb ^ (row & 7)), register accumulators per column, so the end-of-unit reduction is two
       // shuffles and a handful of atomics.  All loads of a stage are issued first and the stage is released
       // before the arithmetic.
+      if (new_job && prev_job >= 0) flush_group(a.jobs[prev_job]);
       const int t = threadIdx.x - 64;
       const int cb = t & 7, rql = (t >> 3) & 3, sw = t >> 5;
       const bool do_bias = job.db != nullptr && !(a.dbg_flags & 1);
@@ -217,9 +323,6 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
 #pragma unroll
       for (int i = 0; i < 2; ++i) off2[i] = (uint32_t)((r2 + i) * 128 + ((cb ^ ((r2 + i) & 7)) << 4));
       const bool bias_on = do_bias && k4 < a_chunks;
-      float bs[8], hs[8], hg[8], hbv[8], hb0 = 0.f, hb1 = 0.f, hb2 = 0.f;
-#pragma unroll
-      for (int e = 0; e < 8; ++e) { bs[e] = 0.f; hs[e] = 0.f; hg[e] = 0.f; hbv[e] = 0.f; }
       auto unpack = [](const uint4& w, float (&f)[8]) {
         f[0] = __uint_as_float(w.x << 16); f[1] = __uint_as_float(w.x & 0xffff0000u);
         f[2] = __uint_as_float(w.y << 16); f[3] = __uint_as_float(w.y & 0xffff0000u);
@@ -296,71 +399,16 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
           }
         }
       }
-      // reduce over the four row groups that live in one warp (lane bits 3, 4), then one atomic per column and warp
-      auto warp_rows_sum = [&](float v) {
-        v += __shfl_xor_sync(0xffffffffu, v, 8);
-        v += __shfl_xor_sync(0xffffffffu, v, 16);
-        return v;
-      };
-      if (do_bias) {   // warp-uniform (k4 depends on the warp only)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float v = warp_rows_sum(bs[e]);
-          if (rql == 0 && k4 < a_chunks) atomicAdd(job.db + k4 * 64 + cb * 8 + e, v);
-        }
-      }
-      if (side == 1) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float v = warp_rows_sum(hs[e]);
-          if (rql == 0) atomicAdd(a.dW_sigma + k4 * 64 + cb * 8 + e, v);
-        }
-        const float vb = warp_rows_sum(hb0);
-        if (k4 == 0 && lane == 0) atomicAdd(a.db_sigma, vb);   // cb = 0 lanes of slice-0 warps cover every row once
-      } else if (side == 2) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float v0 = warp_rows_sum(hs[e]), v1 = warp_rows_sum(hg[e]), v2 = warp_rows_sum(hbv[e]);
-          if (rql == 0) {
-            atomicAdd(a.dW_rgb + k2 * 64 + cb * 8 + e, v0);
-            atomicAdd(a.dW_rgb + 128 + k2 * 64 + cb * 8 + e, v1);
-            atomicAdd(a.dW_rgb + 256 + k2 * 64 + cb * 8 + e, v2);
-          }
-        }
-        const float w0 = warp_rows_sum(hb0), w1 = warp_rows_sum(hb1), w2 = warp_rows_sum(hb2);
-        if (k2 == 0 && lane == 0) { atomicAdd(a.db_rgb, w0); atomicAdd(a.db_rgb + 1, w1); atomicAdd(a.db_rgb + 2, w2); }
-      }
-      // accumulator flush: thread = TMEM lane (n_out within the half); the two warp groups split the column blocks
-      mbar_wait(bar_acc, uq & 1);
-      tc_fence_after();
-      const int q = warp & 3, grp = (warp - 2) >> 2;
-      const int halves = a_chunks >> 1;
-      const int nblk = job.b_mma * 2;  // 32-column blocks
-      const bool vec_ok = (job.ld & 3) == 0 && (reinterpret_cast<uintptr_t>(job.dW) & 15) == 0;
-      for (int hh = 0; hh < halves; ++hh) {
-        float* drow = job.dW + (size_t)(hh * 128 + q * 32 + lane) * job.ld;
-        for (int blk = grp; blk < nblk; blk += 2) {
-          uint32_t v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + hh * 256 + blk * 32, v);
-          tmem_ld_wait();
-          const int ch = blk >> 1, cbase = (blk & 1) * 32;
-          const int valid = job.b_valid[ch] - cbase;
-          float* d = drow + ch * 64 + cbase;
-          if (vec_ok && valid >= 32) {
-#pragma unroll
-            for (int c = 0; c < 32; c += 4)
-              red_add_v4(d + c, __uint_as_float(v[c]), __uint_as_float(v[c + 1]), __uint_as_float(v[c + 2]),
-                         __uint_as_float(v[c + 3]));
-          } else {
-#pragma unroll
-            for (int c = 0; c < 32; ++c)
-              if (c < valid) atomicAdd(d + c, __uint_as_float(v[c]));
-          }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_drained);
+    }
+    if (new_job && prev_job >= 0) ++grp;
+    prev_job = j;
+  }
+  // the last job's accumulators
+  if (prev_job >= 0) {
+    if (warp == 1) {
+      if (lane == 0) umma_commit(bar_acc);
+    } else if (warp >= 2) {
+      flush_group(a.jobs[prev_job]);
     }
   }
   tc_fence_before();
@@ -403,7 +451,7 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
   a.gstash = gstash;
   a.d_sigma = d_sigma; a.dpre = dpre;
   a.dW_sigma = g->sigma_w; a.db_sigma = g->sigma_b; a.dW_rgb = g->rgb_w; a.db_rgb = g->rgb_b;
-  a.unit_counter = unit_counter;
+  a.counters = unit_counter;
   auto H = [](int l) { return kStashH0 + 4 * l; };
   add_job(a, 0, 4, {kStashEnc}, 1, {63}, g->xyz_w[0], 63, g->xyz_b[0], 0, 0);
   for (int l = 1; l < 8; ++l) {
@@ -424,35 +472,40 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
   } else {
     add_job(a, 0, 0, {h7, h7 + 1, h7 + 2, h7 + 3}, 0, {}, nullptr, 0, nullptr, 1, 0);  // sigma head (side work only)
   }
-  // units of about equal duration, ~8 per SM in total; CTAs claim them dynamically
+  // granules of a few tiles, claimed per job; CTAs start spread over the jobs in proportion to the jobs' cost
   int dev = 0, sms = kNumSMs;
   NRF_CUDA(cudaGetDevice(&dev));
   NRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  double total_cost = 0;
   // per-stage cost ~ bytes, with a floor: thin stages are latency- rather than bandwidth-paced
   auto stage_cost = [](const WgradJob& j) { return std::max(5, j.a_chunks + j.b_n); };
+  double total_cost = 0;
   for (int i = 0; i < a.n_jobs; ++i) total_cost += stage_cost(a.jobs[i]);
-  const double unit_cost = std::max(1.0, (double)num_tiles * total_cost / (((a.dbg_flags & 8) ? 2.0 : 8.0) * sms));
-  int unit = 0;
+  // granule = 16 tiles (measured best of 2..64 at 4096 x 64/128 rows), less when a CTA's share of a job is small
+  const long per_cta = (long)num_tiles * a.n_jobs / sms;
+  int tpg = (int)std::max<long>(1, std::min<long>(16, per_cta / 8));
+  if (a.dbg_flags & 8) tpg = 4; else if (a.dbg_flags & 16) tpg = 8; else if (a.dbg_flags & 32) tpg = 32;
+  long total_gran = 0;
   for (int i = 0; i < a.n_jobs; ++i) {
     WgradJob& j = a.jobs[i];
-    int tpu = (int)(unit_cost / stage_cost(j) + 0.5);
-    tpu = std::max(1, std::min(tpu, num_tiles));
-    j.tiles_per_unit = tpu;
-    j.n_units = (num_tiles + tpu - 1) / tpu;
-    j.first_unit = unit;
-    unit += j.n_units;
+    j.tiles_per_gran = std::max(1, std::min(tpg, num_tiles));
+    j.n_gran = (num_tiles + j.tiles_per_gran - 1) / j.tiles_per_gran;
+    total_gran += j.n_gran;
   }
-  a.total_units = unit;
+  const int grid = (int)std::min<long>(total_gran, sms);
+  double cum = 0;
+  for (int i = 0; i < a.n_jobs; ++i) {
+    a.jobs[i].first_cta = (int)(grid * cum / total_cost);
+    cum += stage_cost(a.jobs[i]);
+  }
   static bool configured = false;
   const int smem_bytes = (int)kWgSmTotal + 1024;
   if (!configured) {
     NRF_CUDA(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     configured = true;
   }
-  NRF_CUDA(cudaMemsetAsync(unit_counter, 0, sizeof(int), st));
+  NRF_CUDA(cudaMemsetAsync(unit_counter, 0, kWgMaxJobs * sizeof(int), st));
   ProfScope prof(full ? NRF_K_WGRAD_FULL : NRF_K_WGRAD_SIGMA, st, n_rows);
-  mlp_wgrad_kernel<<<std::min(a.total_units, sms), kWgThreads, smem_bytes, st>>>(a);
+  mlp_wgrad_kernel<<<grid, kWgThreads, smem_bytes, st>>>(a);
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }
