@@ -49,6 +49,10 @@ def ncu_traffic():
         return {}
 
 
+WORKLOAD = ("nerf_pl training step: render_rays fwd+bwd + grad all-reduce, 4096 rays/GPU, N_samples=64 N_importance=64, "
+            "perturb=1 noise_std=1 white_back, NeRF D=8 W=256 random init (optimizer step excluded)")
+
+
 def load_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -130,14 +134,14 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n = 256
+    n = 1024
     reps = max(1, args.steps)
     rate, cores, med = cpu_reference_rate(n, reps)
     line = {"impl": "reference", "metric": "train_rays_per_sec", "value": rate, "unit": "rays/s", "n_gpus": args.gpus,
             "steps": reps, "warmup": 1, "ms_per_step": med * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "render_rays fwd+bwd, 64 coarse + 64 fine samples, Blender-style rays, random-init "
-                                   "NeRF D=8 W=256", "rays_per_step_sample": n},
+            "config": {"workload": WORKLOAD, "rays_per_gpu": RAYS_PER_GPU,
+                       "sample": f"each step = {n} rays of the 4096-ray batch on the host cores (fp32, all threads)"},
             "cpu_baseline": {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
                              "sample": f"{n} rays per step (bounded sample of the 4096-ray batch), median of {reps}"},
             "e2e": {"value": rate, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -310,9 +314,7 @@ def run_gpu(args):
         line = {"metric": "train_rays_per_sec", "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": K,
                 "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
-                "config": {"workload": "nerf_pl training step: render_rays fwd+bwd + grad all-reduce, 4096 rays/GPU, "
-                                       "N_samples=64 N_importance=64, perturb=1 noise_std=1 white_back, NeRF D=8 W=256 "
-                                       "random init (optimizer step excluded)",
+                "config": {"workload": WORKLOAD,
                            "rays_per_gpu": B, "parallelism": f"ray-sharded dp{world}",
                            "l2": "256 MB flush between timed steps; per-step activation traffic >> 126 MB L2",
                            "train_step_flop_per_ray": FLOP_PER_RAY_TRAIN,
@@ -322,9 +324,9 @@ def run_gpu(args):
                         "h2d_bytes_per_step": B * 8 * 4 + B * 3 * 4, "d2h_bytes_per_step": 4},
                 "roofline": roof}
         if world == 1 and not args.no_cpu_baseline:
-            rate, cores, med = cpu_reference_rate(256, 3)
+            rate, cores, med = cpu_reference_rate(1024, 5)
             line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
-                                    "sample": f"256 rays per call (bounded sample of the 4096-ray batch), median of 3, "
+                                    "sample": f"1024 rays per call (bounded sample of the 4096-ray batch), median of 5, "
                                               f"{med:.2f} s per call"}
         print(json.dumps(line), flush=True)
     if world > 1:
