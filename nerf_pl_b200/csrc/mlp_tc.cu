@@ -19,11 +19,13 @@
 // Roofline: tensor pipe (593 408 MAC/sample).  HBM traffic: 32 B/ray in, 16 B/sample
 // out (+5.3 KB/sample stash when training); weights (1.17 MB) stay L2 resident (measured L2 -> SMEM
 // bulk-copy rate with all 148 CTAs on the same blob: > 19 TB/s, tools/stream_bench.py).
+#include <cstdlib>
 #include "common.cuh"
 #include "embed.cuh"
 #include "tc_common.cuh"
 #include "tc_epilogue.cuh"
 #include "tc_layout.cuh"
+#include "tc_fwd.cuh"
 
 namespace nrf {
 namespace tc {
@@ -34,6 +36,14 @@ constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreadsInfer = 64 + kEpiThreads;
 constexpr int kThreadsTrain = kThreadsInfer + 32;   // + the stash store warp
 constexpr uint32_t kTmemCols = 512;
+// Chunks per hand-over: the epilogue announces its output (fence.proxy.async + mbarrier arrive) every kGrp 64-column
+// chunks, and the MMAs of the next layer start per group.  1 = earliest start of the next layer but four fences per
+// layer, during which all epilogue warps of an SM sub-partition stall together; 2 measured best.
+#ifndef NRF_FWD_GRP
+#define NRF_FWD_GRP 2
+#endif
+constexpr int kGrp = NRF_FWD_GRP;
+static_assert(kGrp == 1 || kGrp == 2 || kGrp == 4, "kGrp");
 
 // shared-memory map (dynamic shared memory is declared 1024-byte aligned; no slack is left for re-alignment)
 constexpr uint32_t kSmEnc = 0;                                    // xyz encoding, later direction encoding
@@ -44,38 +54,6 @@ constexpr uint32_t kSmScratch = kSmAux + AuxOffsets::count * 4;  // [4][128][3] 
 constexpr uint32_t kSmBars = kSmScratch + 4 * 128 * 3 * 4;
 constexpr uint32_t kSmTotal = kSmBars + 256;
 static_assert(kSmTotal <= 232448, "shared memory budget");
-
-struct FwdArgs {
-  const uint8_t* packed;
-  const float* rays;
-  const float* z;
-  int64_t n_rows;
-  int S;
-  int num_tiles;
-  float* sigma_out;
-  float* rgb_out;
-  uint8_t* stash;      // training only
-  uint32_t* masks;     // training only
-  unsigned long long* dbg;  // optional per-CTA cycle counters (nrf_dbg_set_counters), null normally
-};
-
-#ifndef NRF_FWD_DEBUG
-#define NRF_FWD_DEBUG 0   // build with NVCC_EXTRA=-DNRF_FWD_DEBUG=1 for the cycle counters / timeline (tools/fwd_*.py)
-#endif
-// Debug timeline (CTA 0 only, when dbg != null): dbg[kTraceBase + role * kTraceCap + n] = clock64() of event n.
-constexpr int kTraceBase = 148 * 8, kTraceCap = 4096;
-#define NRF_TRACE(role, n)                                                                          \
-  do {                                                                                              \
-    if (NRF_FWD_DEBUG && a.dbg && blockIdx.x == 0 && (n) < kTraceCap) a.dbg[kTraceBase + (role) * kTraceCap + (n)++] = clock64(); \
-  } while (0)
-
-// Progress markers (debug build, dbg = PINNED HOST memory so that they survive a trapped launch): the last wait every
-// role of every CTA entered, dbg[kMarkBase + cta * 32 + slot] = code (tools/fwd_deadlock.py decodes them).
-constexpr int kMarkBase = kTraceBase + 4 * kTraceCap;
-#define NRF_MARK(slot, code)                                                                        \
-  do {                                                                                              \
-    if (NRF_FWD_DEBUG && a.dbg) ((volatile unsigned long long*)a.dbg)[kMarkBase + blockIdx.x * 32 + (slot)] = (unsigned long long)(code); \
-  } while (0)
 
 // A-operand readiness barriers: act chunks 0..3, xyz encoding, direction encoding
 constexpr int kBarEnc = 4, kBarDir = 5, kNumBarA = 6;
@@ -210,7 +188,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
             prewait(3);
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {
-              wait_a(c);
+              if (c % kGrp == 0) wait_a(c + kGrp - 1);
               chunk(act_desc + (uint64_t)(c * (kActChunkBytes >> 4)), d_tmem, idesc, first);
               first = false;
             }
@@ -327,7 +305,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
             if (c + 1 < 4) tmem_ld16(t_acc + (c + 1) * 64 + sub * 16, vn);
             const int c0 = c * 64 + sub * 16;
             const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-            acquire(c);
+            if (c % kGrp == 0) acquire(c + kGrp - 1);
             if (L == 7) epi_fwd16<true, kTrain, true>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
             else if (L < 8) epi_fwd16<true, kTrain, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
             else epi_fwd16<false, false, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
@@ -335,8 +313,10 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
               if (c == 1) mw0 = ~mreg; else mw1 = ~mreg;
               mreg = 0;
             }
-            if (feed) signal(c);             // the MMA thread (and, in training, the store warp) take it from here
-            else if (kTrain) signal_store(c);
+            if (c % kGrp == kGrp - 1) {
+              if (feed) signal(c);             // the MMA thread (and, in training, the store warp) take it from here
+              else if (kTrain) signal_store(c);
+            }
             if (et == 0) NRF_TRACE(2, tn2);
           }
           if (kTrain && L < 8)
@@ -389,10 +369,10 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
             }
             if (kTrain) {
               const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-              acquire(c);
+              if (kGrp == 1 || c == 0) acquire(kGrp == 1 ? c : kGrp - 1);
               st_shared_v4(chunk_s + rsw.piece(sub * 2), pk[0], pk[1], pk[2], pk[3]);
               st_shared_v4(chunk_s + rsw.piece(sub * 2 + 1), pk[4], pk[5], pk[6], pk[7]);
-              signal_store(c);
+              if (kGrp == 1 || c == 1) signal_store(kGrp == 1 ? c : kGrp - 1);
             }
           }
           if (kTrain) mask_tile[8 * 128 * 8 + (size_t)row * 4 + sub] = ~mreg;
@@ -422,11 +402,19 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
     uint32_t s_par = 0;
     int pending = -1;
     int mk = 0;
-    auto store = [&](int bar_idx, int buf, const uint8_t* src, uint8_t* dst) {   // bar_idx >= 8: bar_s[bar_idx - 8]
+    auto store = [&](int bar_idx, int buf, const uint8_t* src, uint8_t* dst, uint32_t bytes = kActChunkBytes) {   // bar_idx >= 8: bar_s[bar_idx - 8]
       NRF_MARK(18, 0x6000000 | (mk << 4) | bar_idx);
-      mbar_wait(bar_idx < 8 ? bar_a + bar_idx : bar_s + (bar_idx - 8), (s_par >> bar_idx) & 1u);
+      uint64_t* bar = bar_idx < 8 ? bar_a + bar_idx : bar_s + (bar_idx - 8);
+      const uint32_t par = (s_par >> bar_idx) & 1u;
+      // about to block: hand the pending buffer back first (the epilogue may need it to produce this very image)
+      if (pending >= 0 && !mbar_try_wait(bar, par)) {
+        bulk_wait_read0();
+        mbar_arrive(bar_free + pending);
+        pending = -1;
+      }
+      mbar_wait(bar, par);
       s_par ^= 1u << bar_idx;
-      bulk_s2g(dst, src, kActChunkBytes);
+      bulk_s2g(dst, src, bytes);
       bulk_commit();
       if (pending >= 0) {
         bulk_wait_read1();
@@ -444,7 +432,8 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
         if (L < 9) {
           uint8_t* dst = a.stash + img_off(L < 8 ? kStashH0 + 4 * L : kStashFeat, 4, tile, a.num_tiles);
           const int bar0 = (L + 1 < kLayers) ? 0 : 8;
-          for (int c = 0; c < 4; ++c) store(bar0 + c, c, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes);
+          for (int c = 0; c < 4; c += kGrp)
+            store(bar0 + c + kGrp - 1, c + kGrp - 1, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes, kGrp * kActChunkBytes);
           if (L == 4) {
             if (kFull) store(kBarDir, kFreeEnc, s_enc, a.stash + img_off(kStashDir, 1, tile, a.num_tiles));
             else if (next < a.num_tiles) store(kBarEnc, kFreeEnc, s_enc, a.stash + img_off(kStashEnc, 1, next, a.num_tiles));
@@ -452,7 +441,11 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
         } else {
           if (next < a.num_tiles) store(kBarEnc, kFreeEnc, s_enc, a.stash + img_off(kStashEnc, 1, next, a.num_tiles));
           uint8_t* dst = a.stash + img_off(kStashMid, 2, tile, a.num_tiles);
-          for (int c = 0; c < 2; ++c) store(8 + c, c, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes);
+          if (kGrp == 1) {
+            for (int c = 0; c < 2; ++c) store(8 + c, c, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes);
+          } else {
+            store(8 + kGrp - 1, kGrp - 1, s_act, dst, 2 * kActChunkBytes);
+          }
         }
       }
     }
@@ -495,6 +488,12 @@ static unsigned long long* g_dbg_counters = nullptr;
 // Diagnostics: device buffer of >= 8 * gridDim 64-bit counters filled by the next forward launches (null = off).
 extern "C" void nrf_dbg_set_counters(void* dev_ptr) { g_dbg_counters = static_cast<unsigned long long*>(dev_ptr); }
 
+// NRF_FWD_IMPL=pair selects the CTA-pair kernel (mlp_tc_pair.cu); experimental until it is the default
+static bool use_pair_kernel() {
+  const char* e = getenv("NRF_FWD_IMPL");   // read per call: tools/pair_check.py switches it at run time
+  return e && e[0] == 'p';
+}
+
 extern "C" size_t nrf_mlp_tc_stash_bytes(int64_t rows, int sigma_only) {
   if (rows <= 0) return 0;
   const size_t tiles = (size_t)((rows + kTileM - 1) / kTileM);
@@ -516,6 +515,7 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
   a.num_tiles = (int)((rows + kTileM - 1) / kTileM);
   a.sigma_out = sigma_out; a.rgb_out = rgb_out;
   a.dbg = g_dbg_counters;
+  { const char* e = getenv("NRF_DBG_FLAGS"); a.dbg_flags = (NRF_FWD_DEBUG && e) ? atoi(e) : 0; }
   cudaStream_t st = as_stream(stream);
   if (stash != nullptr) {
     const size_t need = nrf_mlp_tc_stash_bytes(rows, sigma_only);
@@ -525,8 +525,10 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
     }
     a.stash = static_cast<uint8_t*>(stash);
     a.masks = reinterpret_cast<uint32_t*>(a.stash + (size_t)a.num_tiles * stash_tile_bytes(!sigma_only));
+    if (use_pair_kernel()) return launch_fwd_pair(!sigma_only, true, a, st);
     return sigma_only ? launch_fwd<false, true>(a, st) : launch_fwd<true, true>(a, st);
   }
+  if (use_pair_kernel()) return launch_fwd_pair(!sigma_only, false, a, st);
   return sigma_only ? launch_fwd<false, false>(a, st) : launch_fwd<true, false>(a, st);
 }
 

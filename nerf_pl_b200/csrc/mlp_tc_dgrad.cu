@@ -52,6 +52,12 @@ constexpr int kDgNumBarFree = 5;               // same buffers: the G-image stor
 // G0 (nobody but the store warp reads it) is announced on barriers of its own: a parity wait only tells "one completion
 // behind" from "up to date", so every waiter must consume every completion of a barrier
 constexpr int kDgNumBarS = 4;
+// chunks per hand-over (see kGrp in mlp_tc.cu)
+#ifndef NRF_DG_GRP
+#define NRF_DG_GRP 2
+#endif
+constexpr int kDgGrp = NRF_DG_GRP;
+static_assert(kDgGrp == 1 || kDgGrp == 2 || kDgGrp == 4, "kDgGrp");
 
 template <bool kFull>
 __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_constant__ DgradArgs a) {
@@ -135,9 +141,10 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
 #pragma unroll 1
           for (int c = 0; c < nchunks; ++c) {
             const int src = from_pro ? kDgBarPro : c;
-            if (!from_pro || c == 0) {
-              mbar_wait(bar_a + src, (a_par >> src) & 1u);
-              a_par ^= 1u << src;
+            if (from_pro ? c == 0 : (c % kDgGrp == 0)) {
+              const int b = from_pro ? src : c + kDgGrp - 1;
+              mbar_wait(bar_a + b, (a_par >> b) & 1u);
+              a_par ^= 1u << b;
             }
             if (ready == 0) mbar_wait(bar_full + stage, ph); else --ready;
             tc_fence_after();
@@ -236,10 +243,10 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
             pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
           const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-          acquire(c);
+          if (c % kDgGrp == 0) acquire(c + kDgGrp - 1);
           st_shared_v4(chunk_s + rsw.piece(sub * 2), pk[0], pk[1], pk[2], pk[3]);
           st_shared_v4(chunk_s + rsw.piece(sub * 2 + 1), pk[4], pk[5], pk[6], pk[7]);
-          signal(c);
+          if (c % kDgGrp == kDgGrp - 1) signal(c);
         }
       }
       return dsig;
@@ -277,10 +284,12 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
           const int c0 = c * 64 + sub * 16;
           const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
           const uint32_t m = (c < 2) ? mw.x : mw.y;
-          acquire(c);
+          if (c % kDgGrp == 0) acquire(c + kDgGrp - 1);
           if (kFull && t == 7) epi_dgrad16<true>(v, c, c0, m, dsig, wsig_s, rsw, chunk_s, sub * 2);
           else epi_dgrad16<false>(v, c, c0, m, dsig, wsig_s, rsw, chunk_s, sub * 2);
-          if (t > 0) {
+          if (c % kDgGrp != kDgGrp - 1) {
+            // hand-over per group of kDgGrp chunks
+          } else if (t > 0) {
             signal(c);   // the UMMA issuer and the store warp take it from here
           } else {       // G0: the store warp only
             fence_async_smem();
@@ -301,7 +310,15 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
     int pending = -1;
     auto store = [&](int idx, bool own_bar, const uint8_t* src, uint8_t* dst, uint32_t bytes) {
       const int pb = own_bar ? 8 + idx : idx;
-      mbar_wait(own_bar ? bar_s + idx : bar_a + idx, (s_par >> pb) & 1u);
+      uint64_t* bar = own_bar ? bar_s + idx : bar_a + idx;
+      const uint32_t par = (s_par >> pb) & 1u;
+      // about to block: hand the pending buffer back first (the epilogue may need it to produce this very image)
+      if (pending >= 0 && !mbar_try_wait(bar, par)) {
+        bulk_wait_read0();
+        mbar_arrive(bar_free + pending);
+        pending = -1;
+      }
+      mbar_wait(bar, par);
       s_par ^= 1u << pb;
       bulk_s2g(dst, src, bytes);
       bulk_commit();
@@ -313,8 +330,8 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
     };
     auto store_act = [&](int slot, int tile) {
       uint8_t* dst = a.gstash + img_off(slot, 4, tile, a.num_tiles);
-      for (int c = 0; c < 4; ++c)
-        store(c, slot == 0, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes, kActChunkBytes);
+      for (int c = 0; c < 4; c += kDgGrp)
+        store(c + kDgGrp - 1, slot == 0, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes, kDgGrp * kActChunkBytes);
     };
     int tile = blockIdx.x;
     if (kFull && tile < a.num_tiles)

@@ -1,0 +1,47 @@
+// Arguments and debug hooks shared by the forward kernels (mlp_tc.cu: one CTA per tile; mlp_tc_pair.cu: CTA pairs).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace nrf {
+namespace tc {
+
+struct FwdArgs {
+  const uint8_t* packed;
+  const float* rays;
+  const float* z;
+  int64_t n_rows;
+  int S;
+  int num_tiles;
+  float* sigma_out;
+  float* rgb_out;
+  uint8_t* stash;      // training only
+  uint32_t* masks;     // training only
+  unsigned long long* dbg;  // optional per-CTA cycle counters (nrf_dbg_set_counters), null normally
+  int dbg_flags;            // debug build only (NRF_DBG_FLAGS): 1 = issue no MMAs, 2 = epilogue does no arithmetic
+};
+
+#ifndef NRF_FWD_DEBUG
+#define NRF_FWD_DEBUG 0   // build with NVCC_EXTRA=-DNRF_FWD_DEBUG=1 for the cycle counters / timeline (tools/fwd_*.py)
+#endif
+// Debug timeline (CTA 0 only, when dbg != null): dbg[kTraceBase + role * kTraceCap + n] = clock64() of event n.
+constexpr int kTraceBase = 148 * 8, kTraceCap = 4096;
+#define NRF_TRACE(role, n)                                                                          \
+  do {                                                                                              \
+    if (NRF_FWD_DEBUG && a.dbg && blockIdx.x == 0 && (n) < kTraceCap) a.dbg[kTraceBase + (role) * kTraceCap + (n)++] = clock64(); \
+  } while (0)
+
+// Progress markers (debug build, dbg = PINNED HOST memory so that they survive a trapped launch): the last wait every
+// role of every CTA entered, dbg[kMarkBase + cta * 32 + slot] = code (tools/fwd_deadlock.py decodes them).
+constexpr int kMarkBase = kTraceBase + 4 * kTraceCap;
+#define NRF_MARK(slot, code)                                                                        \
+  do {                                                                                              \
+    if (NRF_FWD_DEBUG && a.dbg) ((volatile unsigned long long*)a.dbg)[kMarkBase + blockIdx.x * 32 + (slot)] = (unsigned long long)(code); \
+  } while (0)
+
+
+// CTA-pair forward (mlp_tc_pair.cu)
+int launch_fwd_pair(bool full, bool train, const FwdArgs& a, cudaStream_t st);
+
+}  // namespace tc
+}  // namespace nrf
