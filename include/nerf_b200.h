@@ -197,6 +197,9 @@ void nrf_dbg_set_counters(void* dev_ptr);
 int nrf_dbg_stream(const void* base, unsigned long long cta_stride, unsigned long long stream_stride,
                    unsigned long long tile_stride, uint32_t piece, int n_streams, int ppc, int wrap_tiles,
                    int steps, int stages, int grid, nrf_stream_t stream);
+/* Measurement aid: `grid` CTAs each issue `reps` tcgen05.mma (M=128, N=256, K=16, bf16) back to back; out[cta] (u64,
+ * device) = cycles from the first issue to the completion of the last. */
+int nrf_dbg_mma_rate(int reps, int grid, void* out, nrf_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -55,6 +55,37 @@ __global__ void __launch_bounds__(64, 1) stream_kernel(const __grid_constant__ S
   }
 }
 
+// Measurement aid: cycles per tcgen05.mma (kind::f16, M=128, N=256, K=16, operands from shared memory) when ONE
+// thread issues `reps` of them back to back into two alternating accumulators; out[cta] = total cycles.
+__global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, unsigned long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 2 * 32768);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar + 1);
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < 2 * 32768 / 4; i += 64) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  if (threadIdx.x == 0) { mbar_init(bar, 1); fence_barrier_init(); }
+  if (warp == 1) tmem_alloc(s_tmem, 512);
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+  if (threadIdx.x == 0) {
+    const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
+    const uint64_t a_desc = make_desc_sw128(smem_u32(smem), 16, 1024);
+    const uint64_t b_desc = make_desc_sw128(smem_u32(smem + 32768), 16, 1024);
+    const long long t0 = clock64();
+    for (int r = 0; r < reps; ++r)
+      umma_ss(tmem_base + (r & 1) * 256, a_desc + 2 * (r & 3), b_desc + 2 * (r & 3), idesc, r >= 2);
+    umma_commit(bar);
+    mbar_wait(bar, 0);
+    out[blockIdx.x] = (unsigned long long)(clock64() - t0);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
+}
+
 }  // namespace tc
 }  // namespace nrf
 
@@ -72,6 +103,16 @@ extern "C" int nrf_dbg_stream(const void* base, unsigned long long cta_stride, u
   StreamArgs a{static_cast<const uint8_t*>(base), cta_stride, stream_stride, tile_stride, piece, n_streams, ppc,
                wrap_tiles, steps, stages};
   stream_kernel<<<grid, 64, smem_bytes, as_stream(stream)>>>(a);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+// Launches `grid` CTAs issuing `reps` MMAs each; out (grid x u64, device) receives the cycles each CTA needed.
+extern "C" int nrf_dbg_mma_rate(int reps, int grid, void* out, nrf_stream_t stream) {
+  NRF_REQUIRE(out && reps >= 2 && grid >= 1, "nrf_dbg_mma_rate: bad args");
+  const size_t smem_bytes = 2 * 32768 + 64;
+  NRF_CUDA(cudaFuncSetAttribute(mma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  mma_rate_kernel<<<grid, 64, smem_bytes, as_stream(stream)>>>(reps, static_cast<unsigned long long*>(out));
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

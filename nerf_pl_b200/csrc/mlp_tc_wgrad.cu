@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kWgStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1 + kWgSideWarps); }
+    for (int s = 0; s < kWgStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1 + kWgSideWarps / 2); }
     mbar_init(bar_acc, 1);
     mbar_init(bar_drained, kWgSideWarps);
     for (int s = 0; s < 2; ++s) { mbar_init(bar_uq_full + s, 1); mbar_init(bar_uq_empty + s, 1 + kWgSideWarps); }
@@ -124,10 +124,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
   auto flush_group = [&](const WgradJob& pj) {
     const int t = threadIdx.x - 64;
     const int cb = t & 7, rql = (t >> 3) & 3, sw = t >> 5;
-    const int k4 = sw & 3, k2 = sw & 1;
+    const bool active = (warp & 2) != 0;                // side work runs on the warps of SM sub-partitions 2 and 3 only
+    const int ai = (sw & 1) | ((sw >> 2) << 1);         // 0..3 over the active warps
+    const int k4 = ai, k2 = ai & 1;
     const int a_chunks = pj.a_chunks;
-    const bool do_bias = pj.db != nullptr && !(a.dbg_flags & 1);
-    const int side = (a.dbg_flags & 1) ? 0 : pj.side;
+    const bool do_bias = active && pj.db != nullptr && !(a.dbg_flags & 1);
+    const int side = (!active || (a.dbg_flags & 1)) ? 0 : pj.side;
     // reduce over the four row groups that live in one warp (lane bits 3, 4), then one atomic per column and warp
     auto warp_rows_sum = [&](float v) {
       v += __shfl_xor_sync(0xffffffffu, v, 8);
@@ -310,18 +312,33 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       // shuffles and a handful of atomics.  All loads of a stage are issued first and the stage is released
       // before the arithmetic.
       if (new_job && prev_job >= 0) flush_group(a.jobs[prev_job]);
+      // The arithmetic of the side work competes for issue slots with whatever shares its SM sub-partition; the
+      // producer and the UMMA issuer (warps 0, 1) are latency critical, so only the side warps of sub-partitions 2
+      // and 3 (warp & 2) do it (measured: -0.1 ms per step); the others only help with the accumulator flush.
+      const bool active = (warp & 2) != 0;
+      if (!active) {
+        it += n_stage;
+      } else {
       const int t = threadIdx.x - 64;
       const int cb = t & 7, rql = (t >> 3) & 3, sw = t >> 5;
+      const int ai = (sw & 1) | ((sw >> 2) << 1);       // 0..3 over the active warps
       const bool do_bias = job.db != nullptr && !(a.dbg_flags & 1);
       const int side = (a.dbg_flags & 1) ? 0 : job.side;
-      // bias / sigma head: slice k4 = sw & 3, rows r4 .. r4+3;  rgb head: slice k2 = sw & 1, rows r2, r2+1
-      const int k4 = sw & 3, r4 = ((sw >> 2) * 4 + rql) * 4;
-      const int k2 = sw & 1, r2 = ((sw >> 1) * 4 + rql) * 2;
-      uint32_t off4[4], off2[2];
+      // bias / sigma head: slice k4 = ai, rows rql*4 .. +3 and the same +16;  rgb head: slice k2 = ai & 1, rows
+      // ((ai >> 1) * 8 + rql * 2) .. +1 and the same +16
+      const int k4 = ai;
+      const int k2 = ai & 1;
+      uint32_t off4[8], off2[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) off4[i] = (uint32_t)((r4 + i) * 128 + ((cb ^ ((r4 + i) & 7)) << 4));
+      for (int i = 0; i < 8; ++i) {
+        const int r = rql * 4 + (i & 3) + (i >> 2) * 16;
+        off4[i] = (uint32_t)(r * 128 + ((cb ^ (r & 7)) << 4));
+      }
 #pragma unroll
-      for (int i = 0; i < 2; ++i) off2[i] = (uint32_t)((r2 + i) * 128 + ((cb ^ ((r2 + i) & 7)) << 4));
+      for (int i = 0; i < 4; ++i) {
+        const int r = (ai >> 1) * 8 + rql * 2 + (i & 1) + (i >> 1) * 16;
+        off2[i] = (uint32_t)(r * 128 + ((cb ^ (r & 7)) << 4));
+      }
       const bool bias_on = do_bias && k4 < a_chunks;
       auto unpack = [](const uint4& w, float (&f)[8]) {
         f[0] = __uint_as_float(w.x << 16); f[1] = __uint_as_float(w.x & 0xffff0000u);
@@ -333,32 +350,38 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
         const int tile = t0 + (s >> 2), rs = s & 3;
         const uint32_t stage = it % kWgStages, ph = (it / kWgStages) & 1;
         const int64_t row0 = (int64_t)tile * kTileM + rs * kWgSliceRows;
-        float ds[4] = {0.f, 0.f, 0.f, 0.f};
-        float4 dp[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+        float ds[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        float4 dp[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dp[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (side == 1) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) ds[i] = (row0 + r4 + i < a.n_rows) ? __ldg(a.d_sigma + row0 + r4 + i) : 0.f;
+          for (int i = 0; i < 8; ++i) {
+            const int64_t r = row0 + rql * 4 + (i & 3) + (i >> 2) * 16;
+            ds[i] = (r < a.n_rows) ? __ldg(a.d_sigma + r) : 0.f;
+          }
         } else if (side == 2) {
 #pragma unroll
-          for (int i = 0; i < 2; ++i) dp[i] = __ldg(reinterpret_cast<const float4*>(a.dpre) + row0 + r2 + i);
+          for (int i = 0; i < 4; ++i)
+            dp[i] = __ldg(reinterpret_cast<const float4*>(a.dpre) + row0 + (ai >> 1) * 8 + rql * 2 + (i & 1) + (i >> 1) * 16);
         }
         mbar_wait(bar_full + stage, ph);
         const uint8_t* st = smem + stage * kWgStageBytes;
-        uint4 gw[4], xw[4];
+        uint4 gw[8], xw[8];
         uint32_t dep = 0;
         if (bias_on) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { gw[i] = *reinterpret_cast<const uint4*>(st + k4 * kWgSlice + off4[i]); dep ^= gw[i].w; }
+          for (int i = 0; i < 8; ++i) { gw[i] = *reinterpret_cast<const uint4*>(st + k4 * kWgSlice + off4[i]); dep ^= gw[i].w; }
         }
         if (side == 1) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
+          for (int i = 0; i < 8; ++i) {
             xw[i] = *reinterpret_cast<const uint4*>(st + (kWgASlots + job.side_off + k4) * kWgSlice + off4[i]);
             dep ^= xw[i].w;
           }
         } else if (side == 2) {
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
+          for (int i = 0; i < 4; ++i) {
             xw[i] = *reinterpret_cast<const uint4*>(st + (kWgASlots + job.side_off + k2) * kWgSlice + off2[i]);
             dep ^= xw[i].w;
           }
@@ -368,10 +391,11 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
         if (dep == 0x5bd1e995u) s_unit[2] = (int)dep;   // s_unit[2]: scratch word nobody reads
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_empty + stage);
+        if (a.dbg_flags & 4) continue;   // experiment: loads only, no arithmetic
         float f[8];
         if (bias_on) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
+          for (int i = 0; i < 8; ++i) {
             unpack(gw[i], f);
 #pragma unroll
             for (int e = 0; e < 8; ++e) bs[e] += f[e];
@@ -379,7 +403,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
         }
         if (side == 1) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
+          for (int i = 0; i < 8; ++i) {
             unpack(xw[i], f);
 #pragma unroll
             for (int e = 0; e < 8; ++e) hs[e] = fmaf(ds[i], f[e], hs[e]);
@@ -387,7 +411,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
           }
         } else if (side == 2) {
 #pragma unroll
-          for (int i = 0; i < 2; ++i) {
+          for (int i = 0; i < 4; ++i) {
             unpack(xw[i], f);
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
@@ -399,6 +423,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
           }
         }
       }
+      }   // active
     }
     if (new_job && prev_job >= 0) ++grp;
     prev_job = j;
