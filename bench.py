@@ -168,6 +168,8 @@ def run_gpu(args):
     import nerf_pl_b200
     from nerf_pl_b200 import _lib
     from nerf_pl_b200.dist import GradBucket
+    from nerf_pl_b200.losses import loss_dict
+    from nerf_pl_b200.datasets.ray_utils import gen_rays
     from nerf_pl_b200.mlp import forward_rays
     from nerf_pl_b200.models.nerf import Embedding, NeRF
     from nerf_pl_b200.models.rendering import render_rays
@@ -185,6 +187,7 @@ def run_gpu(args):
         models.append(m)
     emb = [Embedding(3, 10), Embedding(3, 4)]
     bucket = GradBucket(models)
+    mse_loss = loss_dict["mse"]()          # losses.py:4-14, fused: one launch forward, one backward
 
     B = RAYS_PER_GPU
     all_rays = O.blender_rays(B * world, seed=1)
@@ -196,7 +199,7 @@ def run_gpu(args):
     def step(rays_d, rgbs_d):
         bucket.zero()
         out = render_rays(models, emb, rays_d, NC, False, 1.0, 1.0, NF, 1024 * 32, True)
-        loss = ((out["rgb_coarse"] - rgbs_d) ** 2).mean() + ((out["rgb_fine"] - rgbs_d) ** 2).mean()   # losses.py:9-14
+        loss = mse_loss(out, rgbs_d)
         loss.backward()
         bucket.allreduce_mean()
         return loss
@@ -309,6 +312,28 @@ def run_gpu(args):
                                          "ms_per_launch": k_ms, "tflops": ach, "peak": peaks["bf16_burst"],
                                          "frac": ach / peaks["bf16_burst"]}
 
+    # ---- the rows either side of the path, HBM-bound streaming kernels, timed alone ---------
+    def timed(fn, reps=20):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    c2w = torch.tensor([[0.6, -0.48, 0.64, 2.56], [0.8, 0.36, -0.48, -1.92], [0.0, 0.8, 0.6, 2.4]])
+    t_rays = timed(lambda: gen_rays(c2w, 800, 800, 1111.0, 2.0, 6.0, device=dev))
+    pa, pt = torch.rand(640000, 3, device=dev), torch.rand(640000, 3, device=dev)
+    from nerf_pl_b200.losses import mse_pair
+    t_mse = timed(lambda: mse_pair(pa, None, pt))
+    side_rows = {"gen_rays_800x800": {"ms": t_rays, "gbs": 640000 * 32 / (t_rays * 1e-3) / 1e9, "bytes": 640000 * 32},
+                 "mse_800x800x3": {"ms": t_mse, "gbs": 640000 * 3 * 8 / (t_mse * 1e-3) / 1e9, "bytes": 640000 * 3 * 8},
+                 "note": "20 MB and 15 MB working sets: launch-latency bound, far below the 6.5 TB/s copy bandwidth"}
+
     if rank == 0:
         rays_per_s = world * B / (ms * 1e-3)
         line = {"metric": "train_rays_per_sec", "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": K,
@@ -322,7 +347,7 @@ def run_gpu(args):
                 "clocks": clocks, "gpu_launches": launches,
                 "e2e": {"value": world * B / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": B * 8 * 4 + B * 3 * 4, "d2h_bytes_per_step": 4},
-                "roofline": roof}
+                "roofline": roof, "side_rows": side_rows}
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, med = cpu_reference_rate(1024, 5)
             line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",

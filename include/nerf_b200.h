@@ -55,6 +55,25 @@ uint64_t nrf_launch_count(void);
 int nrf_prof_enable(int on);
 int nrf_prof_read(int kernel_id, double* total_ms, int64_t* launches, int64_t* rows);
 
+/* a21 camera-ray generation — datasets/ray_utils.py:5-93 (get_ray_directions, get_rays, get_ndc_rays) fused with the
+ * datasets' row assembly (datasets/blender.py:80-84).  c2w: HOST pointer to the 3x4 camera-to-world matrix (row-major);
+ * pix (n) device int64 flat pixel indices row*W+col, or NULL for the first n pixels in row-major order;
+ * rays_out (n,8) = [o, d/|d|, near, far].  ndc != 0: rays are mapped to NDC with the near plane `near_plane`
+ * (ray_utils.py:52-93) and the depth bounds written are [0, 1] (datasets/llff.py:236-239). */
+int nrf_gen_rays(const float* c2w, int H, int W, float focal, const int64_t* pix, int64_t n, float near_plane,
+                 float far_plane, int ndc, float* rays_out, nrf_stream_t stream);
+
+/* a22 fused MSE — losses.py:4-26 (MSELoss / SMMSELoss: mean((a-t)^2) [+ mean((b-t)^2)]) and metrics.py:4-10 (mse with an
+ * optional element mask).  pred_b, mask may be NULL; mask is one byte per element (non-zero = counted).  One launch,
+ * deterministic (fixed summation order); loss_out (1) device float.  workspace: nrf_mse_workspace_bytes() bytes, zeroed
+ * once by the caller (the kernel leaves it reusable).  nrf_mse_pair_bwd writes 2 (x - t) / n_elems * upstream[0]
+ * for each non-NULL gradient (no mask). */
+size_t nrf_mse_workspace_bytes(void);
+int nrf_mse_pair(const float* pred_a, const float* pred_b, const float* target, const uint8_t* mask, int64_t n_elems,
+                 float* loss_out, void* workspace, nrf_stream_t stream);
+int nrf_mse_pair_bwd(const float* pred_a, const float* pred_b, const float* target, int64_t n_elems, const float* upstream,
+                     float* grad_a, float* grad_b, nrf_stream_t stream);
+
 /* a4  stratified depth sampling — models/rendering.py:216-232
  * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);
  * u (N,n_samples) uniform [0,1) or NULL (required iff perturb > 0); z_out (N,n_samples). */

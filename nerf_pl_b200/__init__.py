@@ -16,4 +16,9 @@ def install_as_models():
         sys.modules[f"models.{sub}"] = importlib.import_module(f"nerf_pl_b200.models.{sub}")
     ts = importlib.import_module("nerf_pl_b200.torchsearchsorted")
     sys.modules.setdefault("torchsearchsorted", ts)
+    # the steps either side of the path: ray generation, losses, metrics
+    sys.modules.setdefault("losses", importlib.import_module("nerf_pl_b200.losses"))
+    sys.modules.setdefault("metrics", importlib.import_module("nerf_pl_b200.metrics"))
+    # (datasets/ray_utils.py: import nerf_pl_b200.datasets.ray_utils from the dataset classes; the reference's `datasets`
+    #  package itself -- file formats, kornia -- stays the caller's)
     return pkg

@@ -35,6 +35,10 @@ SIGNATURES = {
     "nrf_launch_count": (ctypes.c_uint64, []),
     "nrf_prof_enable": (I, [I]),
     "nrf_prof_read": (I, [I, P, P, P]),
+    "nrf_gen_rays": (I, [P, I, I, F, P, L, F, F, I, P, P]),
+    "nrf_mse_workspace_bytes": (Z, []),
+    "nrf_mse_pair": (I, [P, P, P, P, L, P, P, P]),
+    "nrf_mse_pair_bwd": (I, [P, P, P, L, P, P, P, P]),
     "nrf_sample_coarse": (I, [P, P, L, I, I, F, P, P, P]),
     "nrf_embed_fwd": (I, [P, L, I, P, I, P, P]),
     "nrf_embed_bwd": (I, [P, P, L, I, P, I, P, P]),

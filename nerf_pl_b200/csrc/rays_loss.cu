@@ -1,0 +1,193 @@
+// The steps either side of render_rays: camera-ray generation on the GPU and the fused MSE loss.
+//
+//   a21 nrf_gen_rays     datasets/ray_utils.py:5-93 (get_ray_directions + get_rays + get_ndc_rays) and the row
+//                        assembly of the datasets (datasets/blender.py:80-84: [o, d, near, far]) in one pass:
+//                        no (H,W,3) direction grid, no rays_o/rays_d temporaries, nothing crosses PCIe but 12 floats.
+//   a22 nrf_mse_pair     losses.py:4-14 (MSELoss / SMMSELoss: mean((a-t)^2) + mean((b-t)^2)) and metrics.py:4-10
+//                        (mse with an optional mask) as ONE deterministic reduction launch;
+//       nrf_mse_pair_bwd the gradients 2 (x - t) / n * upstream for both predictions in one launch.
+// Both are HBM-bound streaming kernels: 32 B written per ray; 12 (24) B read per element of the loss.
+#include <cmath>
+#include "common.cuh"
+
+namespace nrf {
+
+struct C2W { float m[12]; };   // row-major 3x4, by value in the kernel parameters
+
+__global__ void gen_rays_kernel(const __grid_constant__ C2W c2w, int H, int W, float focal, const int64_t* __restrict__ pix,
+                                int64_t n, float near, float far, int ndc, float* __restrict__ rays) {
+  const float half_w = (float)W / 2.0f, half_h = (float)H / 2.0f;   // W/2, H/2 (python true division)
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < n; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t p = pix ? __ldg(pix + idx) : idx;
+    const float i = (float)(p % W), j = (float)(p / W);              // grid x (column), y (row): ray_utils.py:17-18
+    // ray_utils.py:21-22 (no +0.5 pixel centre)
+    const float dx = __fdiv_rn(__fsub_rn(i, half_w), focal);
+    const float dy = -__fdiv_rn(__fsub_rn(j, half_h), focal);
+    const float dz = -1.0f;
+    // ray_utils.py:43: directions @ c2w[:, :3].T, accumulated left to right
+    float d[3], o[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      d[k] = __fadd_rn(__fadd_rn(__fmul_rn(dx, c2w.m[k * 4 + 0]), __fmul_rn(dy, c2w.m[k * 4 + 1])), __fmul_rn(dz, c2w.m[k * 4 + 2]));
+      o[k] = c2w.m[k * 4 + 3];                                      // ray_utils.py:46
+    }
+    const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(d[0], d[0]), __fmul_rn(d[1], d[1])), __fmul_rn(d[2], d[2])));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) d[k] = __fdiv_rn(d[k], nrm);        // ray_utils.py:44
+    if (ndc) {                                                      // ray_utils.py:75-91 with the scalar near plane
+      const float t = __fdiv_rn(-__fadd_rn(near, o[2]), d[2]);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) o[k] = __fadd_rn(o[k], __fmul_rn(t, d[k]));
+      const float ox_oz = __fdiv_rn(o[0], o[2]), oy_oz = __fdiv_rn(o[1], o[2]);
+      const float sx = __fdiv_rn(-1.0f, __fdiv_rn((float)W, __fmul_rn(2.0f, focal)));
+      const float sy = __fdiv_rn(-1.0f, __fdiv_rn((float)H, __fmul_rn(2.0f, focal)));
+      const float o0 = __fmul_rn(sx, ox_oz), o1 = __fmul_rn(sy, oy_oz);
+      const float o2 = __fadd_rn(1.0f, __fdiv_rn(__fmul_rn(2.0f, near), o[2]));
+      const float d0 = __fmul_rn(sx, __fsub_rn(__fdiv_rn(d[0], d[2]), ox_oz));
+      const float d1 = __fmul_rn(sy, __fsub_rn(__fdiv_rn(d[1], d[2]), oy_oz));
+      const float d2 = __fsub_rn(1.0f, o2);
+      o[0] = o0; o[1] = o1; o[2] = o2; d[0] = d0; d[1] = d1; d[2] = d2;
+    }
+    float4* out = reinterpret_cast<float4*>(rays + idx * 8);
+    out[0] = make_float4(o[0], o[1], o[2], d[0]);
+    out[1] = make_float4(d[1], d[2], ndc ? 0.0f : near, ndc ? 1.0f : far);   // datasets/llff.py:236-239: NDC rays span [0, 1]
+  }
+}
+
+// ---- fused MSE ---------------------------------------------------------------------------------
+constexpr int kMseThreads = 512;
+
+__device__ __forceinline__ double block_sum(double v, double* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  double r = 0.0;
+  if (threadIdx.x == 0)
+    for (int w = 0; w < kMseThreads / 32; ++w) r += sh[w];
+  __syncthreads();
+  return r;   // valid in thread 0
+}
+
+// partial[cta] = {sum (a-t)^2, sum (b-t)^2, count}; the CTA that takes the last ticket adds the partials in index
+// order (deterministic) and writes loss = sum_a / count (+ sum_b / count).  `ticket` is left at zero.
+__global__ void __launch_bounds__(kMseThreads) mse_pair_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                               const float* __restrict__ t, const uint8_t* __restrict__ mask,
+                                                               int64_t n, double* __restrict__ partial,
+                                                               unsigned int* __restrict__ ticket, float* __restrict__ loss) {
+  __shared__ double sh[kMseThreads / 32];
+  __shared__ bool last;
+  double sa = 0.0, sb = 0.0, cnt = 0.0;
+  int64_t first = 0;
+  const bool vec = !mask && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(t) |
+                              (b ? reinterpret_cast<uintptr_t>(b) : 0)) & 15) == 0;
+  if (vec) {   // 16-byte loads over the aligned body; fp32 partial sums of 4 squares, fp64 across iterations
+    const int64_t n4 = n >> 2;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+      const float4 tv = __ldg(reinterpret_cast<const float4*>(t) + i), av = __ldg(reinterpret_cast<const float4*>(a) + i);
+      const float d0 = av.x - tv.x, d1 = av.y - tv.y, d2 = av.z - tv.z, d3 = av.w - tv.w;
+      sa += (double)d0 * d0 + (double)d1 * d1 + (double)d2 * d2 + (double)d3 * d3;
+      if (b) {
+        const float4 bv = __ldg(reinterpret_cast<const float4*>(b) + i);
+        const float e0 = bv.x - tv.x, e1 = bv.y - tv.y, e2 = bv.z - tv.z, e3 = bv.w - tv.w;
+        sb += (double)e0 * e0 + (double)e1 * e1 + (double)e2 * e2 + (double)e3 * e3;
+      }
+      cnt += 4.0;
+    }
+    first = n4 << 2;
+  }
+  for (int64_t i = first + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (mask && !mask[i]) continue;
+    const float tv = __ldg(t + i);
+    const float da = __fsub_rn(__ldg(a + i), tv);
+    sa += (double)__fmul_rn(da, da);
+    if (b) {
+      const float db = __fsub_rn(__ldg(b + i), tv);
+      sb += (double)__fmul_rn(db, db);
+    }
+    cnt += 1.0;
+  }
+  const double ra = block_sum(sa, sh), rb = block_sum(sb, sh), rc = block_sum(cnt, sh);
+  if (threadIdx.x == 0) {
+    partial[blockIdx.x * 3 + 0] = ra;
+    partial[blockIdx.x * 3 + 1] = rb;
+    partial[blockIdx.x * 3 + 2] = rc;
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    __threadfence();
+    double ta = 0.0, tb = 0.0, tc = 0.0;
+    for (unsigned int c = 0; c < gridDim.x; ++c) {
+      ta += __ldcg(partial + c * 3 + 0);   // written by other SMs: read through L2
+      tb += __ldcg(partial + c * 3 + 1);
+      tc += __ldcg(partial + c * 3 + 2);
+    }
+    float l = (float)(ta / tc);          // nan for an empty selection, like torch.mean of an empty tensor
+    if (b) l = __fadd_rn(l, (float)(tb / tc));
+    *loss = l;
+    *ticket = 0u;
+  }
+}
+
+__global__ void mse_pair_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ t,
+                                    int64_t n, const float* __restrict__ upstream, float* __restrict__ ga,
+                                    float* __restrict__ gb) {
+  const float s = __fdiv_rn(__fmul_rn(2.0f, __ldg(upstream)), (float)n);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float tv = __ldg(t + i);
+    if (ga) ga[i] = __fmul_rn(s, __fsub_rn(__ldg(a + i), tv));
+    if (gb) gb[i] = __fmul_rn(s, __fsub_rn(__ldg(b + i), tv));
+  }
+}
+
+}  // namespace nrf
+
+using namespace nrf;
+
+extern "C" int nrf_gen_rays(const float* c2w, int H, int W, float focal, const int64_t* pix, int64_t n, float near_plane,
+                            float far_plane, int ndc, float* rays_out, nrf_stream_t stream) {
+  NRF_REQUIRE(H >= 1 && W >= 1 && focal > 0.f && n >= 0, "nrf_gen_rays: bad sizes");
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(c2w && rays_out, "nrf_gen_rays: null pointer");
+  NRF_REQUIRE(pix || n <= (int64_t)H * W, "nrf_gen_rays: more rays than pixels");
+  C2W m;
+  for (int i = 0; i < 12; ++i) m.m[i] = c2w[i];
+  const int threads = 256;
+  const int64_t want = (n + threads - 1) / threads;
+  const int blocks = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
+  gen_rays_kernel<<<blocks, threads, 0, as_stream(stream)>>>(m, H, W, focal, pix, n, near_plane, far_plane, ndc, rays_out);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" size_t nrf_mse_workspace_bytes(void) { return (size_t)kNumSMs * 3 * sizeof(double) + 16; }
+
+extern "C" int nrf_mse_pair(const float* pred_a, const float* pred_b, const float* target, const uint8_t* mask,
+                            int64_t n_elems, float* loss_out, void* workspace, nrf_stream_t stream) {
+  NRF_REQUIRE(n_elems >= 0, "nrf_mse_pair: bad size");
+  NRF_REQUIRE(pred_a && target && loss_out && workspace, "nrf_mse_pair: null pointer");
+  double* partial = static_cast<double*>(workspace);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(partial + (size_t)kNumSMs * 3);
+  const int64_t want = (n_elems + kMseThreads * 8 - 1) / (kMseThreads * 8);
+  const int blocks = (int)(want < 1 ? 1 : (want < kNumSMs ? want : kNumSMs));
+  mse_pair_kernel<<<blocks, kMseThreads, 0, as_stream(stream)>>>(pred_a, pred_b, target, mask, n_elems, partial, ticket, loss_out);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" int nrf_mse_pair_bwd(const float* pred_a, const float* pred_b, const float* target, int64_t n_elems,
+                                const float* upstream, float* grad_a, float* grad_b, nrf_stream_t stream) {
+  NRF_REQUIRE(n_elems >= 0, "nrf_mse_pair_bwd: bad size");
+  if (n_elems == 0) return NRF_OK;
+  NRF_REQUIRE(target && upstream && (grad_a || grad_b), "nrf_mse_pair_bwd: null pointer");
+  NRF_REQUIRE((!grad_a || pred_a) && (!grad_b || pred_b), "nrf_mse_pair_bwd: gradient without its prediction");
+  const int threads = 256;
+  const int64_t want = (n_elems + threads - 1) / threads;
+  const int blocks = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
+  mse_pair_bwd_kernel<<<blocks, threads, 0, as_stream(stream)>>>(pred_a, pred_b, target, n_elems, upstream, grad_a, grad_b);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}

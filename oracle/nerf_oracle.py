@@ -419,3 +419,65 @@ def make_noise(n: int, nc: int, nf: int, seed: int = 2, perturb: bool = True) ->
         out["jitter_fine"] = torch.rand(n, nf, generator=g)
         out["noise_fine"] = torch.randn(n, nc + nf, generator=g)
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# The steps either side of the path: ray generation, MSE loss, psnr
+# --------------------------------------------------------------------------------------------
+
+def get_ray_directions(H: int, W: int, focal: float) -> Tensor:
+    """datasets/ray_utils.py:5-24.  kornia.create_meshgrid(H, W, normalized_coordinates=False) is
+    x = 0..W-1 along columns, y = 0..H-1 along rows (kornia 0.2.0 utils/grid.py), restated with arange."""
+    i = torch.arange(W, dtype=torch.float32).expand(H, W)
+    j = torch.arange(H, dtype=torch.float32).unsqueeze(1).expand(H, W)
+    return torch.stack([(i - W / 2) / focal, -(j - H / 2) / focal, -torch.ones_like(i)], -1)
+
+
+def get_rays(directions: Tensor, c2w: Tensor) -> Tuple[Tensor, Tensor]:
+    """datasets/ray_utils.py:27-51"""
+    rays_d = directions @ c2w[:, :3].T
+    rays_d = rays_d / torch.norm(rays_d, dim=-1, keepdim=True)
+    rays_o = c2w[:, 3].expand(rays_d.shape)
+    return rays_o.reshape(-1, 3), rays_d.reshape(-1, 3)
+
+
+def get_ndc_rays(H: int, W: int, focal: float, near, rays_o: Tensor, rays_d: Tensor) -> Tuple[Tensor, Tensor]:
+    """datasets/ray_utils.py:52-93"""
+    t = -(near + rays_o[..., 2]) / rays_d[..., 2]
+    rays_o = rays_o + t[..., None] * rays_d
+    ox_oz = rays_o[..., 0] / rays_o[..., 2]
+    oy_oz = rays_o[..., 1] / rays_o[..., 2]
+    o0 = -1. / (W / (2. * focal)) * ox_oz
+    o1 = -1. / (H / (2. * focal)) * oy_oz
+    o2 = 1. + 2. * near / rays_o[..., 2]
+    d0 = -1. / (W / (2. * focal)) * (rays_d[..., 0] / rays_d[..., 2] - ox_oz)
+    d1 = -1. / (H / (2. * focal)) * (rays_d[..., 1] / rays_d[..., 2] - oy_oz)
+    d2 = 1 - o2
+    return torch.stack([o0, o1, o2], -1), torch.stack([d0, d1, d2], -1)
+
+
+def dataset_rays(c2w: Tensor, H: int, W: int, focal: float, near: float, far: float, ndc: bool = False) -> Tensor:
+    """The (H*W, 8) rows a dataset hands to render_rays: datasets/blender.py:80-84; datasets/llff.py:232-245
+    (NDC: get_ndc_rays with near plane `near`, depth bounds [0, 1])."""
+    o, d = get_rays(get_ray_directions(H, W, focal), c2w)
+    if ndc:
+        o, d = get_ndc_rays(H, W, focal, near, o, d)
+        near, far = 0.0, 1.0
+    one = torch.ones_like(o[:, :1])
+    return torch.cat([o, d, near * one, far * one], 1)
+
+
+def mse_loss(inputs: Dict[str, Tensor], targets: Tensor, prefix: str = "rgb") -> Tensor:
+    """losses.py:4-26 (MSELoss for prefix 'rgb', SMMSELoss for 'sm')"""
+    loss = torch.mean((inputs[f"{prefix}_coarse"] - targets) ** 2)
+    if f"{prefix}_fine" in inputs:
+        loss = loss + torch.mean((inputs[f"{prefix}_fine"] - targets) ** 2)
+    return loss
+
+
+def psnr(image_pred: Tensor, image_gt: Tensor, valid_mask: Optional[Tensor] = None) -> Tensor:
+    """metrics.py:4-13"""
+    value = (image_pred - image_gt) ** 2
+    if valid_mask is not None:
+        value = value[valid_mask]
+    return -10 * torch.log10(torch.mean(value))

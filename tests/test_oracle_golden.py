@@ -137,3 +137,47 @@ def test_camera_algebra_matches_reference():
                                torch.from_numpy(c["light_camera"]), torch.from_numpy(c["light_eye"]))
     np.testing.assert_allclose(R.numpy(), c["R01"], rtol=1e-6, atol=1e-7)
     np.testing.assert_allclose(Q.numpy(), c["Q01"], rtol=1e-6, atol=1e-7)
+
+
+# ---- the rows either side of the path: ray generation, MSE loss, psnr -------------------
+
+def _rays_loss():
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rays_loss.npz"))
+
+
+@pytest.mark.parametrize("name", ["blender_small", "fork_bounds", "llff_ndc"])
+def test_oracle_ray_generation_vs_reference(name):
+    """oracle get_ray_directions / get_rays / get_ndc_rays / dataset rows == datasets/ray_utils.py run by
+    tests/make_golden_rays.py (same torch ops: bit-exact)."""
+    z = _rays_loss()
+    H, W, focal, near, far, ndc = z[f"{name}/hwf"]
+    H, W, ndc = int(H), int(W), bool(ndc)
+    c2w = torch.from_numpy(z[f"{name}/c2w"])
+    d = O.get_ray_directions(H, W, float(focal))
+    np.testing.assert_array_equal(d.numpy(), z[f"{name}/directions"])
+    o, dd = O.get_rays(d, c2w)
+    np.testing.assert_array_equal(o.numpy(), z[f"{name}/rays_o"])
+    np.testing.assert_array_equal(dd.numpy(), z[f"{name}/rays_d"])
+    if ndc:
+        no, nd = O.get_ndc_rays(H, W, float(focal), float(near), o, dd)
+        np.testing.assert_array_equal(no.numpy(), z[f"{name}/ndc_o"])
+        np.testing.assert_array_equal(nd.numpy(), z[f"{name}/ndc_d"])
+    rays = O.dataset_rays(c2w, H, W, float(focal), float(near), float(far), ndc)
+    np.testing.assert_array_equal(rays.numpy(), z[f"{name}/rays"])
+
+
+@pytest.mark.parametrize("name", ["loss_small", "loss_batch"])
+def test_oracle_mse_psnr_vs_reference(name):
+    z = _rays_loss()
+    a = torch.from_numpy(z[f"{name}/a"]).requires_grad_()
+    b = torch.from_numpy(z[f"{name}/b"]).requires_grad_()
+    t = torch.from_numpy(z[f"{name}/t"])
+    loss = O.mse_loss({"rgb_coarse": a, "rgb_fine": b}, t)
+    loss.backward()
+    np.testing.assert_allclose(loss.detach().numpy(), z[f"{name}/mse2"], rtol=1e-6)
+    np.testing.assert_allclose(a.grad.numpy(), z[f"{name}/ga"], rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(b.grad.numpy(), z[f"{name}/gb"], rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(O.mse_loss({"rgb_coarse": a.detach()}, t).numpy(), z[f"{name}/mse1"], rtol=1e-6)
+    np.testing.assert_allclose(O.mse_loss({"sm_coarse": a.detach(), "sm_fine": b.detach()}, t, "sm").numpy(), z[f"{name}/sm2"], rtol=1e-6)
+    np.testing.assert_allclose(O.psnr(a.detach(), t).numpy(), z[f"{name}/psnr"], rtol=1e-6)
+    np.testing.assert_allclose(O.psnr(a.detach(), t, torch.from_numpy(z[f"{name}/mask"])).numpy(), z[f"{name}/psnr_masked"], rtol=1e-6)
