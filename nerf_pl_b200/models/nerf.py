@@ -80,3 +80,35 @@ class NeRF(nn.Module):
         if not x.is_cuda:
             raise RuntimeError("nerf_pl_b200.NeRF needs CUDA tensors (no CPU path)")
         return _mlp.MlpEmbedded.apply(x, self._spec, bool(sigma_only), *self.ordered_parameters())
+
+    @torch.no_grad()
+    def query(self, xyz, dirs=None, sigma_only=False, chunk=1 << 22):
+        """Query-mode evaluation on arbitrary points (dense-grid sigma for mesh extraction,
+        extract_color_mesh.py:120-133; per-vertex colour queries :195-270): xyz (B,3) [, dirs (B,3), default zeros as
+        the reference passes] -> (B,4) [rgb, sigma] or (B,1) sigma, no autograd.  Positional encodings
+        (Embedding(3,10) / Embedding(3,4)) are computed inside the tensor-core kernel; the points are handed over as
+        one-sample rays o = xyz, d = dirs, z = 0 (o + d * 0 is exact), so the (B,63|90) embedding never exists."""
+        if not xyz.is_cuda:
+            raise RuntimeError("nerf_pl_b200.NeRF needs CUDA tensors (no CPU path)")
+        if xyz.dim() != 2 or xyz.shape[1] != 3 or (dirs is not None and dirs.shape != xyz.shape):
+            raise RuntimeError("query expects xyz (B,3) and dirs (B,3)")
+        B = xyz.shape[0]
+        precision = _ops.get_mlp_precision()
+        params = [p.detach() for p in self.ordered_parameters()]
+        packed = self.packed_weights() if (precision == "bf16" and self._spec.tc_capable) else None
+        out = torch.empty(B, 1 if sigma_only else 4, device=xyz.device, dtype=torch.float32)
+        for i in range(0, B, chunk):
+            n = min(chunk, B - i)
+            rays = torch.zeros(n, 8, device=xyz.device, dtype=torch.float32)
+            rays[:, 0:3] = xyz[i:i + n]
+            if dirs is not None:
+                rays[:, 3:6] = dirs[i:i + n]
+            z = torch.zeros(n, 1, device=xyz.device, dtype=torch.float32)
+            sigma, rgb, _ = _mlp.forward_rays(self._spec, params, rays, z, bool(sigma_only), False, precision, packed=packed)
+            if sigma_only:
+                out[i:i + n] = sigma
+            else:
+                out[i:i + n, 0:3] = rgb.view(n, 3)
+                out[i:i + n, 3:4] = sigma
+        return out
+

@@ -341,3 +341,36 @@ def test_grad_bucket_direct_sinks_match_autograd(dev, precision):
         assert torch.equal(bucket.flat[off:off + first.numel()], flat_before[off:off + first.numel()])
     finally:
         nerf_pl_b200.set_mlp_precision("bf16")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-5), ("bf16", 2e-2)])
+def test_query_points_vs_oracle(dev, precision, tol):
+    """Query-mode MLP (dense-grid sigma of extract_color_mesh.py:113-133 and coloured point queries) against the oracle
+    NeRF.forward on Embedding outputs: relative to the output scale, 2e-5 (fp32 kernels) / 2e-2 (bf16 tensor cores, raw
+    sigma is unbounded and not squashed by a sigmoid); zero directions as in the reference; a ragged size with chunking."""
+    import nerf_pl_b200
+    from nerf_pl_b200.models.nerf import NeRF
+    nerf_pl_b200.set_mlp_precision(precision)
+    try:
+        p = O.init_mlp_params(generator=torch.Generator().manual_seed(3))
+        m = NeRF().to(dev)
+        m.load_state_dict(p)
+        N = 21
+        lin = np.linspace(-1.2, 1.2, N)
+        xyz = torch.tensor(np.stack(np.meshgrid(lin, lin, lin), -1).reshape(-1, 3), dtype=torch.float32)   # :117-123
+        dirs = torch.zeros_like(xyz)
+        ref = O.mlp_forward(p, torch.cat([O.embed(xyz, 10), O.embed(dirs, 4)], 1))
+        got = m.query(xyz.to(dev), chunk=4000).cpu()
+        assert got.shape == (N ** 3, 4)
+        scale = ref.abs().max().item()
+        assert (got - ref).abs().max().item() <= tol * scale, (got - ref).abs().max().item() / scale
+        sig = m.query(xyz.to(dev), sigma_only=True).cpu()
+        assert sig.shape == (N ** 3, 1) and (sig[:, 0] - ref[:, 3]).abs().max().item() <= tol * scale
+        d2 = torch.nn.functional.normalize(torch.randn(500, 3, generator=torch.Generator().manual_seed(1)), dim=-1)
+        ref2 = O.mlp_forward(p, torch.cat([O.embed(xyz[:500], 10), O.embed(d2, 4)], 1))
+        got2 = m.query(xyz[:500].to(dev), d2.to(dev)).cpu()
+        assert (got2 - ref2).abs().max().item() <= tol * scale
+        assert m.query(xyz[:0].to(dev)).shape == (0, 4)
+    finally:
+        nerf_pl_b200.set_mlp_precision("bf16")
