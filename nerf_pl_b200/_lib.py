@@ -62,6 +62,7 @@ SIGNATURES = {
     "nrf_normed_w": (I, [P, P, P, P, L, P, P]),
     "nrf_dbg_set_counters": (None, [P]),
     "nrf_dbg_mma_rate": (I, [I, I, P, P]),
+    "nrf_dbg_store_rate": (I, [P, ctypes.c_uint64, c_uint32, I, I, I, P, P]),
     "nrf_dbg_stream": (I, [P, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, c_uint32, I, I, I, I, I, I, P]),
     "nrf_shadow_bwd": (I, [P, P, P, P, P, P, P, P, P, L, I, I, I, F, F, F, F, I, P, P, P, P, Z, P]),
 }

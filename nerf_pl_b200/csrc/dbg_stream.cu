@@ -55,6 +55,30 @@ __global__ void __launch_bounds__(64, 1) stream_kernel(const __grid_constant__ S
   }
 }
 
+// Measurement aid: bulk STORE rate shared memory -> global (the stash path of the forward / dgrad kernels).  One thread
+// per CTA issues `steps` cp.async.bulk stores of `piece` bytes from a constant smem buffer to consecutive addresses,
+// keeping `depth` groups in flight; out[cta] = cycles.
+__global__ void __launch_bounds__(32, 1) store_rate_kernel(uint8_t* dst, unsigned long long cta_stride, uint32_t piece,
+                                                           int steps, int depth, unsigned long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  for (uint32_t i = threadIdx.x; i < piece / 4; i += 32) reinterpret_cast<uint32_t*>(smem)[i] = i;
+  fence_async_smem();
+  __syncwarp();
+  if (threadIdx.x == 0) {
+    uint8_t* p = dst + (size_t)blockIdx.x * cta_stride;
+    const long long t0 = clock64();
+    for (int s = 0; s < steps; ++s) {
+      bulk_s2g(p + (size_t)s * piece, smem, piece);
+      bulk_commit();
+      if (depth == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      else if (depth == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      else asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
+    }
+    bulk_wait_all0();
+    out[blockIdx.x] = (unsigned long long)(clock64() - t0);
+  }
+}
+
 // Measurement aid: cycles per tcgen05.mma (kind::f16, M=128, N=256, K=16, operands from shared memory) when ONE
 // thread issues `reps` of them back to back into two alternating accumulators; out[cta] = total cycles.
 __global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, unsigned long long* out) {
@@ -113,6 +137,17 @@ extern "C" int nrf_dbg_mma_rate(int reps, int grid, void* out, nrf_stream_t stre
   const size_t smem_bytes = 2 * 32768 + 64;
   NRF_CUDA(cudaFuncSetAttribute(mma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   mma_rate_kernel<<<grid, 64, smem_bytes, as_stream(stream)>>>(reps, static_cast<unsigned long long*>(out));
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+// `grid` CTAs each store steps x piece bytes (piece <= 64 KB, multiple of 16) starting at dst + cta * cta_stride.
+extern "C" int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint32_t piece, int steps, int depth, int grid,
+                                  void* out, nrf_stream_t stream) {
+  NRF_REQUIRE(dst && out && piece % 16 == 0 && piece >= 16 && piece <= 65536 && steps >= 1 && grid >= 1, "nrf_dbg_store_rate: bad args");
+  NRF_CUDA(cudaFuncSetAttribute(store_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+  store_rate_kernel<<<grid, 32, 65536, as_stream(stream)>>>(static_cast<uint8_t*>(dst), cta_stride, piece, steps, depth,
+                                                           static_cast<unsigned long long*>(out));
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }
