@@ -50,7 +50,7 @@ def ncu_traffic():
 
 
 WORKLOAD = ("nerf_pl training step: render_rays fwd+bwd + grad all-reduce, 4096 rays/GPU, N_samples=64 N_importance=64, "
-            "perturb=1 noise_std=1 white_back, NeRF D=8 W=256 random init (optimizer step excluded)")
+            "perturb=1 noise_std=1 white_back, NeRF D=8 W=256 random init, Adam(lr=5e-4) step + bf16 operand re-pack included")
 
 
 def load_peaks():
@@ -116,13 +116,16 @@ def cpu_reference_rate(n_rays, reps, threads=None):
             v.requires_grad_()
     rays = O.blender_rays(n_rays, seed=1)
     noise = O.make_noise(n_rays, NC, NF, seed=2)
+    opt = torch.optim.Adam([v for p in params for v in p.values()], lr=5e-4, eps=1e-8)   # utils/__init__.py:17-19
     times = []
     for i in range(reps + 1):
         t0 = time.perf_counter()
+        opt.zero_grad()
         out = O.render_rays(params, rays, n_samples=NC, perturb=1.0, noise_std=1.0, n_importance=NF, white_back=True,
                             noise=noise)
         loss = ((out["rgb_coarse"] - 0.5) ** 2).mean() + ((out["rgb_fine"] - 0.5) ** 2).mean()
         loss.backward()
+        opt.step()
         if i > 0:      # first call is warm-up
             times.append(time.perf_counter() - t0)
     times.sort()
@@ -169,6 +172,7 @@ def run_gpu(args):
     from nerf_pl_b200 import _lib
     from nerf_pl_b200.dist import GradBucket
     from nerf_pl_b200.losses import loss_dict
+    from nerf_pl_b200.optim import FusedAdam
     from nerf_pl_b200.datasets.ray_utils import gen_rays
     from nerf_pl_b200.mlp import forward_rays
     from nerf_pl_b200.models.nerf import Embedding, NeRF
@@ -187,6 +191,7 @@ def run_gpu(args):
         models.append(m)
     emb = [Embedding(3, 10), Embedding(3, 4)]
     bucket = GradBucket(models)
+    opt = FusedAdam(models, lr=5e-4, bucket=bucket)      # utils/__init__.py:17-19; one launch over the flat buffers
     mse_loss = loss_dict["mse"]()          # losses.py:4-14, fused: one launch forward, one backward
 
     B = RAYS_PER_GPU
@@ -197,11 +202,12 @@ def run_gpu(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
     def step(rays_d, rgbs_d):
-        bucket.zero()
-        out = render_rays(models, emb, rays_d, NC, False, 1.0, 1.0, NF, 1024 * 32, True)
+        opt.zero_grad()
+        out = render_rays(models, emb, rays_d, NC, False, 1.0, 1.0, NF, 1024 * 32, True)   # re-packs the stepped weights
         loss = mse_loss(out, rgbs_d)
         loss.backward()
         bucket.allreduce_mean()
+        opt.step()
         return loss
 
     def sync_all():
@@ -330,7 +336,12 @@ def run_gpu(args):
     pa, pt = torch.rand(640000, 3, device=dev), torch.rand(640000, 3, device=dev)
     from nerf_pl_b200.losses import mse_pair
     t_mse = timed(lambda: mse_pair(pa, None, pt))
-    side_rows = {"gen_rays_800x800": {"ms": t_rays, "gbs": 640000 * 32 / (t_rays * 1e-3) / 1e9, "bytes": 640000 * 32},
+    n_par = opt.flat_param.numel()
+    shadow = FusedAdam([NeRF().to(dev), NeRF().to(dev)], lr=5e-4)       # a throw-away twin: timing must not train `models`
+    t_adam = timed(lambda: shadow.step())
+    side_rows = {"adam_step": {"ms": t_adam, "gbs": n_par * 28 / (t_adam * 1e-3) / 1e9, "bytes": n_par * 28,
+                               "params": n_par},
+                 "gen_rays_800x800": {"ms": t_rays, "gbs": 640000 * 32 / (t_rays * 1e-3) / 1e9, "bytes": 640000 * 32},
                  "mse_800x800x3": {"ms": t_mse, "gbs": 640000 * 3 * 8 / (t_mse * 1e-3) / 1e9, "bytes": 640000 * 3 * 8},
                  "note": "20 MB and 15 MB working sets: launch-latency bound, far below the 6.5 TB/s copy bandwidth"}
 

@@ -74,6 +74,11 @@ int nrf_mse_pair(const float* pred_a, const float* pred_b, const float* target, 
 int nrf_mse_pair_bwd(const float* pred_a, const float* pred_b, const float* target, int64_t n_elems, const float* upstream,
                      float* grad_a, float* grad_b, nrf_stream_t stream);
 
+/* a23 fused Adam — torch.optim.Adam as constructed by utils/__init__.py:17-19 (L2 weight decay added to
+ * the gradient, bias-corrected, no amsgrad) over flat fp32 buffers of n elements; `step` counts from 1. */
+int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                  float beta2, float eps, float weight_decay, int64_t step, nrf_stream_t stream);
+
 /* a4  stratified depth sampling — models/rendering.py:216-232
  * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);
  * u (N,n_samples) uniform [0,1) or NULL (required iff perturb > 0); z_out (N,n_samples). */

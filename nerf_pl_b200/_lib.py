@@ -39,6 +39,7 @@ SIGNATURES = {
     "nrf_mse_workspace_bytes": (Z, []),
     "nrf_mse_pair": (I, [P, P, P, P, L, P, P, P]),
     "nrf_mse_pair_bwd": (I, [P, P, P, L, P, P, P, P]),
+    "nrf_adam_step": (I, [P, P, P, P, L, F, F, F, F, F, L, P]),
     "nrf_sample_coarse": (I, [P, P, L, I, I, F, P, P, P]),
     "nrf_embed_fwd": (I, [P, L, I, P, I, P, P]),
     "nrf_embed_bwd": (I, [P, P, L, I, P, I, P, P]),

@@ -191,3 +191,42 @@ extern "C" int nrf_mse_pair_bwd(const float* pred_a, const float* pred_b, const 
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }
+
+// ---- a23 fused Adam over the flat parameter / gradient buffers ----------------------------
+// torch.optim.Adam as the reference constructs it (utils/__init__.py:17-19: lr, eps = 1e-8, weight_decay as an L2 term
+// added to the gradient; betas default (0.9, 0.999); no amsgrad).  One launch for all parameters of all models: they
+// live in ONE flat fp32 buffer (optim.FusedAdam), next to the flat gradient buffer the backward kernels accumulate into.
+namespace nrf {
+__global__ void adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                 float* __restrict__ v, int64_t n, float lr, float beta1, float beta2, float eps,
+                                 float weight_decay, float bias_c1, float bias_c2_sqrt) {
+  const float step_size = lr / bias_c1;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float pv = p[i];
+    float gv = g[i];
+    if (weight_decay != 0.f) gv = fmaf(weight_decay, pv, gv);            // grad.add(param, alpha=weight_decay)
+    const float mv = fmaf(1.0f - beta1, gv - m[i], m[i]);                // exp_avg.lerp_(grad, 1 - beta1)
+    const float vv = fmaf(1.0f - beta2, gv * gv, beta2 * v[i]);          // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+    const float denom = sqrtf(vv) / bias_c2_sqrt + eps;
+    m[i] = mv;
+    v[i] = vv;
+    p[i] = pv - step_size * (mv / denom);                                // param.addcdiv_(exp_avg, denom, value=-step_size)
+  }
+}
+}  // namespace nrf
+
+extern "C" int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                             float beta1, float beta2, float eps, float weight_decay, int64_t step, nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0 && step >= 1, "nrf_adam_step: bad size or step");
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(param && grad && exp_avg && exp_avg_sq, "nrf_adam_step: null pointer");
+  const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
+  const int threads = 256;
+  const int64_t want = (n + threads - 1) / threads;
+  const int blocks = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
+  adam_step_kernel<<<blocks, threads, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
+                                                               weight_decay, (float)bc1, (float)std::sqrt(bc2));
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}

@@ -1,0 +1,74 @@
+"""Fused optimizer step over flat buffers (reference utils/__init__.py:10-30, `--optimizer adam`).
+
+`FusedAdam` re-homes every parameter of the given modules into ONE flat fp32 buffer (p.data becomes a view) and shares
+the flat gradient buffer of a `dist.GradBucket`, so a step is one elementwise launch over 2 x 595 844 values instead of
+torch's per-tensor (or foreach) kernels, and `zero_grad()` is one fill.  It is a torch.optim.Optimizer, so the reference's
+schedulers (`MultiStepLR`, `CosineAnnealingLR`, `GradualWarmupScheduler`, utils/__init__.py:32-49) drive `param_groups`
+as usual.  The bf16 operand images are re-packed lazily by NeRF.packed_weights() when the parameters' version changes."""
+import torch
+
+from . import _lib
+from .dist import GradBucket
+from .ops import _p, _stream
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, bucket=None):
+        modules = list(modules)
+        self.bucket = bucket if bucket is not None else GradBucket(modules)
+        params = self.bucket.params
+        if any(not p.is_cuda or p.dtype != torch.float32 for p in params):
+            raise RuntimeError("FusedAdam needs fp32 CUDA parameters (no CPU path)")
+        n = self.bucket.flat.numel()
+        self.flat_param = torch.empty(n, dtype=torch.float32, device=self.bucket.flat.device)
+        off = 0
+        with torch.no_grad():
+            for p in params:
+                view = self.flat_param[off:off + p.numel()].view_as(p)
+                view.copy_(p)
+                p.data = view
+                off += p.numel()
+        self.exp_avg = torch.zeros_like(self.flat_param)
+        self.exp_avg_sq = torch.zeros_like(self.flat_param)
+        self._steps = 0
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+
+    def zero_grad(self, set_to_none=False):
+        self.bucket.zero()
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        g = self.param_groups[0]
+        self._steps += 1
+        with torch.cuda.device(self.flat_param.device):
+            _lib.call("nrf_adam_step", _p(self.flat_param), _p(self.bucket.flat), _p(self.exp_avg), _p(self.exp_avg_sq),
+                      self.flat_param.numel(), float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
+                      float(g["weight_decay"]), self._steps, _stream())
+        # parameter version counters drive the weight re-pack cache (NeRF.packed_weights); the kernel wrote through
+        # the flat buffer, so bump them here (one C++ call, no launches)
+        torch.autograd.graph.increment_version(self.bucket.params)
+        return loss
+
+    def state_dict(self):
+        return {"steps": self._steps, "flat_param": self.flat_param, "exp_avg": self.exp_avg,
+                "exp_avg_sq": self.exp_avg_sq, "param_groups": [{k: v for k, v in g.items() if k != "params"}
+                                                                  for g in self.param_groups]}
+
+    def load_state_dict(self, sd):
+        self._steps = int(sd["steps"])
+        with torch.no_grad():
+            self.flat_param.copy_(sd["flat_param"])
+            self.exp_avg.copy_(sd["exp_avg"])
+            self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        for g, s in zip(self.param_groups, sd["param_groups"]):
+            g.update(s)
+        torch.autograd.graph.increment_version(self.bucket.params)
+
+
+def get_optimizer(hparams, models):
+    """utils/__init__.py:10-30 for the optimizer this path fuses (`--optimizer adam`, the reference's default);
+    sgd / radam / ranger stay torch-side and are refused here rather than silently substituted."""
+    if getattr(hparams, "optimizer", "adam") != "adam":
+        raise ValueError("nerf_pl_b200.optim fuses 'adam' only; build other optimizers with torch.optim")
+    return FusedAdam(models, lr=hparams.lr, eps=1e-8, weight_decay=getattr(hparams, "weight_decay", 0.0))

@@ -481,3 +481,18 @@ def psnr(image_pred: Tensor, image_gt: Tensor, valid_mask: Optional[Tensor] = No
     if valid_mask is not None:
         value = value[valid_mask]
     return -10 * torch.log10(torch.mean(value))
+
+
+def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, step: int, lr: float,
+              betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0):
+    """One step of the optimizer utils/__init__.py:17-19 constructs: `Adam(parameters, lr, eps=1e-8, weight_decay)`.
+    The algorithm lives in the reference's third-party dependency torch (requirements.txt pins torch==1.4.0): Kingma & Ba
+    Adam with the weight decay folded into the gradient (L2, not decoupled), bias correction on both moments, no amsgrad.
+    Restated here; tests pin it against torch.optim.Adam of the installed torch.  Returns (param, exp_avg, exp_avg_sq)."""
+    b1, b2 = betas
+    g = grad + weight_decay * param if weight_decay != 0 else grad
+    m = b1 * exp_avg + (1 - b1) * g
+    v = b2 * exp_avg_sq + (1 - b2) * g * g
+    step_size = lr / (1 - b1 ** step)
+    denom = v.sqrt() / math.sqrt(1 - b2 ** step) + eps
+    return param - step_size * m / denom, m, v

@@ -181,3 +181,40 @@ def test_oracle_mse_psnr_vs_reference(name):
     np.testing.assert_allclose(O.mse_loss({"sm_coarse": a.detach(), "sm_fine": b.detach()}, t, "sm").numpy(), z[f"{name}/sm2"], rtol=1e-6)
     np.testing.assert_allclose(O.psnr(a.detach(), t).numpy(), z[f"{name}/psnr"], rtol=1e-6)
     np.testing.assert_allclose(O.psnr(a.detach(), t, torch.from_numpy(z[f"{name}/mask"])).numpy(), z[f"{name}/psnr_masked"], rtol=1e-6)
+
+
+def _adam():
+    return np.load(os.path.join(G, "adam.npz"))
+
+
+@pytest.mark.parametrize("name", ["wd0", "wd1e-4"])
+def test_oracle_adam_vs_torch_golden(name):
+    """oracle.adam_step against five recorded torch.optim.Adam steps (tests/make_golden_adam.py).  fp32 evaluation
+    order differs from torch's lerp/addcdiv formulation, so the bar is a few ulp of the update, not bit-exact."""
+    z = _adam()
+    p = torch.from_numpy(z[f"{name}.p0"])
+    m = torch.zeros_like(p)
+    v = torch.zeros_like(p)
+    lr, wd = float(z[f"{name}.lr"]), float(z[f"{name}.weight_decay"])
+    for t in range(z[f"{name}.grads"].shape[0]):
+        p, m, v = O.adam_step(p, torch.from_numpy(z[f"{name}.grads"][t]), m, v, t + 1, lr, eps=1e-8, weight_decay=wd)
+        want = torch.from_numpy(z[f"{name}.params"][t])
+        assert torch.allclose(p, want, rtol=0, atol=4e-7 * lr / 5e-4), (t, (p - want).abs().max())
+    # moments are signed sums: the error scales with the largest gradient seen per element, not with the sum
+    gmax = torch.from_numpy(np.abs(z[f"{name}.grads"]).max(0)) + wd * 1.0
+    assert ((m - torch.from_numpy(z[f"{name}.exp_avg"])).abs() <= 1e-6 * gmax).all()
+    assert ((v - torch.from_numpy(z[f"{name}.exp_avg_sq"])).abs() <= 1e-6 * gmax * gmax).all()
+
+
+def test_oracle_adam_vs_live_torch():
+    """Same restatement against the installed torch.optim.Adam on a fresh seed (pins the golden file's generator)."""
+    g = torch.Generator().manual_seed(5)
+    p = torch.nn.Parameter(torch.randn(1000, generator=g))
+    opt = torch.optim.Adam([p], lr=1e-3, eps=1e-8, weight_decay=1e-2)
+    q, m, v = p.detach().clone(), torch.zeros(1000), torch.zeros(1000)
+    for t in range(3):
+        gr = torch.randn(1000, generator=g)
+        p.grad = gr.clone()
+        opt.step()
+        q, m, v = O.adam_step(q, gr, m, v, t + 1, 1e-3, eps=1e-8, weight_decay=1e-2)
+        assert torch.allclose(q, p.detach(), rtol=0, atol=1e-6)
