@@ -75,9 +75,10 @@ int nrf_mse_pair_bwd(const float* pred_a, const float* pred_b, const float* targ
                      float* grad_a, float* grad_b, nrf_stream_t stream);
 
 /* a23 fused Adam — torch.optim.Adam as constructed by utils/__init__.py:17-19 (L2 weight decay added to
- * the gradient, bias-corrected, no amsgrad) over flat fp32 buffers of n elements; `step` counts from 1. */
-int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
-                  float beta2, float eps, float weight_decay, int64_t step, nrf_stream_t stream);
+ * the gradient, bias-corrected, no amsgrad) over flat fp32 buffers of n elements; `step` counts from 1.  Hyper-parameters
+ * are doubles, rounded to fp32 the way torch rounds its Python scalars (beta and 1 - beta separately). */
+int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr, double beta1,
+                  double beta2, double eps, double weight_decay, int64_t step, nrf_stream_t stream);
 
 /* a4  stratified depth sampling — models/rendering.py:216-232
  * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);

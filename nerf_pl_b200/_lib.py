@@ -2,7 +2,7 @@
 missing or a call fails, a RuntimeError is raised."""
 import ctypes
 import os
-from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_void_p
+from ctypes import POINTER, Structure, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libnerf_b200.so")
@@ -24,7 +24,7 @@ class MlpGrads(Structure):
                 ("sigma_w", c_void_p), ("sigma_b", c_void_p), ("rgb_w", c_void_p), ("rgb_b", c_void_p)]
 
 
-P, I, L, F, Z = c_void_p, c_int, c_int64, c_float, c_size_t
+P, I, L, F, Z, D = c_void_p, c_int, c_int64, c_float, c_size_t, c_double
 PP, PG = POINTER(MlpParams), POINTER(MlpGrads)
 
 # name -> (restype, argtypes); mirrors include/nerf_b200.h declaration by declaration
@@ -39,7 +39,7 @@ SIGNATURES = {
     "nrf_mse_workspace_bytes": (Z, []),
     "nrf_mse_pair": (I, [P, P, P, P, L, P, P, P]),
     "nrf_mse_pair_bwd": (I, [P, P, P, L, P, P, P, P]),
-    "nrf_adam_step": (I, [P, P, P, P, L, F, F, F, F, F, L, P]),
+    "nrf_adam_step": (I, [P, P, P, P, L, D, D, D, D, D, L, P]),
     "nrf_sample_coarse": (I, [P, P, L, I, I, F, P, P, P]),
     "nrf_embed_fwd": (I, [P, L, I, P, I, P, P]),
     "nrf_embed_bwd": (I, [P, P, L, I, P, I, P, P]),

@@ -196,37 +196,69 @@ extern "C" int nrf_mse_pair_bwd(const float* pred_a, const float* pred_b, const 
 // torch.optim.Adam as the reference constructs it (utils/__init__.py:17-19: lr, eps = 1e-8, weight_decay as an L2 term
 // added to the gradient; betas default (0.9, 0.999); no amsgrad).  One launch for all parameters of all models: they
 // live in ONE flat fp32 buffer (optim.FusedAdam), next to the flat gradient buffer the backward kernels accumulate into.
+// Hyper-parameters arrive as doubles and are rounded the way torch rounds its Python scalars: beta and (1 - beta)
+// separately, so (1 - 0.999) is 0.001f and not 1.0f - 0.999f.
 namespace nrf {
-__global__ void adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                                 float* __restrict__ v, int64_t n, float lr, float beta1, float beta2, float eps,
-                                 float weight_decay, float bias_c1, float bias_c2_sqrt) {
-  const float step_size = lr / bias_c1;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const float pv = p[i];
-    float gv = g[i];
-    if (weight_decay != 0.f) gv = fmaf(weight_decay, pv, gv);            // grad.add(param, alpha=weight_decay)
-    const float mv = fmaf(1.0f - beta1, gv - m[i], m[i]);                // exp_avg.lerp_(grad, 1 - beta1)
-    const float vv = fmaf(1.0f - beta2, gv * gv, beta2 * v[i]);          // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
-    const float denom = sqrtf(vv) / bias_c2_sqrt + eps;
-    m[i] = mv;
-    v[i] = vv;
-    p[i] = pv - step_size * (mv / denom);                                // param.addcdiv_(exp_avg, denom, value=-step_size)
+struct AdamK {
+  float step_size, beta2, eps, weight_decay, w1, w2, bc2_sqrt;
+};
+
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamK& k) {
+  if (k.weight_decay != 0.f) g = fmaf(k.weight_decay, p, g);           // grad.add(param, alpha=weight_decay)
+  m = fmaf(k.w1, g - m, m);                                              // exp_avg.lerp_(grad, 1 - beta1)
+  v = fmaf(k.w2, g * g, k.beta2 * v);                                    // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+  const float denom = sqrtf(v) / k.bc2_sqrt + k.eps;                    // (exp_avg_sq.sqrt() / bias_correction2_sqrt).add_(eps)
+  p = p - k.step_size * (m / denom);                                     // param.addcdiv_(exp_avg, denom, value=-step_size)
+}
+
+__global__ void __launch_bounds__(256) adam_step_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                        float* __restrict__ m, float* __restrict__ v, int64_t n, AdamK k) {
+  const int64_t n4 = n >> 2;
+  const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < n4; i += nth) {                              // 16-byte lanes: 4 loads in flight per thread
+    float4 pv = reinterpret_cast<float4*>(p)[i], mv = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
+    const float4 gv = __ldg(reinterpret_cast<const float4*>(g) + i);
+    adam_one(pv.x, gv.x, mv.x, vv.x, k);
+    adam_one(pv.y, gv.y, mv.y, vv.y, k);
+    adam_one(pv.z, gv.z, mv.z, vv.z, k);
+    adam_one(pv.w, gv.w, mv.w, vv.w, k);
+    reinterpret_cast<float4*>(p)[i] = pv;
+    reinterpret_cast<float4*>(m)[i] = mv;
+    reinterpret_cast<float4*>(v)[i] = vv;
   }
+  for (int64_t i = (n4 << 2) + tid; i < n; i += nth) adam_one(p[i], g[i], m[i], v[i], k);
+}
+
+__global__ void __launch_bounds__(256) adam_step_scalar_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                               float* __restrict__ m, float* __restrict__ v, int64_t n, AdamK k) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    adam_one(p[i], g[i], m[i], v[i], k);
 }
 }  // namespace nrf
 
-extern "C" int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
-                             float beta1, float beta2, float eps, float weight_decay, int64_t step, nrf_stream_t stream) {
+extern "C" int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr,
+                             double beta1, double beta2, double eps, double weight_decay, int64_t step,
+                             nrf_stream_t stream) {
   NRF_REQUIRE(n >= 0 && step >= 1, "nrf_adam_step: bad size or step");
   if (n == 0) return NRF_OK;
   NRF_REQUIRE(param && grad && exp_avg && exp_avg_sq, "nrf_adam_step: null pointer");
-  const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
-  const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
+  const double bc1 = 1.0 - std::pow(beta1, (double)step);
+  const double bc2 = 1.0 - std::pow(beta2, (double)step);
+  nrf::AdamK k;
+  k.step_size = (float)(lr / bc1);
+  k.beta2 = (float)beta2;
+  k.eps = (float)eps;
+  k.weight_decay = (float)weight_decay;
+  k.w1 = (float)(1.0 - beta1);
+  k.w2 = (float)(1.0 - beta2);
+  k.bc2_sqrt = (float)std::sqrt(bc2);
   const int threads = 256;
-  const int64_t want = (n + threads - 1) / threads;
+  const bool vec = ((reinterpret_cast<uintptr_t>(param) | reinterpret_cast<uintptr_t>(grad) |
+                     reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0;
+  const int64_t want = ((vec ? (n + 3) / 4 : n) + threads - 1) / threads;
   const int blocks = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
-  adam_step_kernel<<<blocks, threads, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
-                                                               weight_decay, (float)bc1, (float)std::sqrt(bc2));
+  if (vec) nrf::adam_step_kernel<<<blocks, threads, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, k);
+  else nrf::adam_step_scalar_kernel<<<blocks, threads, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, k);
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

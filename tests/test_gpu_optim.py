@@ -65,7 +65,8 @@ def test_fused_adam_trains_like_torch_adam(dev):
     the same steps driven by torch.optim.Adam on a twin model pair; parameters must agree to Adam-update precision and
     the packed bf16 operand images must follow the update (version bump)."""
     import copy
-    from nerf_pl_b200 import Embedding, NeRF, render_rays
+    from nerf_pl_b200.models.nerf import Embedding, NeRF
+    from nerf_pl_b200.models.rendering import render_rays
     from nerf_pl_b200.losses import loss_dict
     from nerf_pl_b200.optim import FusedAdam
     torch.manual_seed(3)
