@@ -173,6 +173,7 @@ def run_gpu(args):
     from nerf_pl_b200.dist import GradBucket
     from nerf_pl_b200.losses import loss_dict
     from nerf_pl_b200.optim import FusedAdam
+    from nerf_pl_b200.graph import GraphedStep
     from nerf_pl_b200.datasets.ray_utils import gen_rays
     from nerf_pl_b200.mlp import forward_rays
     from nerf_pl_b200.models.nerf import Embedding, NeRF
@@ -191,7 +192,8 @@ def run_gpu(args):
         models.append(m)
     emb = [Embedding(3, 10), Embedding(3, 4)]
     bucket = GradBucket(models)
-    opt = FusedAdam(models, lr=5e-4, bucket=bucket)      # utils/__init__.py:17-19; one launch over the flat buffers
+    # utils/__init__.py:17-19; one launch over the flat buffers; step count / lr on the device so the step can be graphed
+    opt = FusedAdam(models, lr=5e-4, bucket=bucket, capturable=True)
     mse_loss = loss_dict["mse"]()          # losses.py:4-14, fused: one launch forward, one backward
 
     B = RAYS_PER_GPU
@@ -224,7 +226,7 @@ def run_gpu(args):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    # ---- device-resident timing --------------------------------------------------------------------
+    # ---- eager pass: per-kernel CUDA-event pairs for the roofline, launch count -----------------------------
     launches0 = lib.nrf_launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     sync_all()
@@ -237,29 +239,37 @@ def run_gpu(args):
     sync_all()
     lib.nrf_prof_enable(0)
     launches = (lib.nrf_launch_count() - launches0) / K
+    ms_eager = sum(a.elapsed_time(b) for a, b in ev) / K
+    # ---- device-resident timing: the same step captured once into a CUDA graph (graph.GraphedStep, the public API for
+    # a fixed-shape training step) and replayed with one launch per step; inputs already in HBM ----------------------
+    graphed = GraphedStep(step, (rays_dev, rgbs_dev), warmup=2, optimizers=[opt])
+    for _ in range(2):
+        graphed(rays_host, rgbs_host)
+    sync_all()
+    for i in range(K):
+        flush.zero_()
+        ev[i][0].record()
+        graphed(*graphed.static_in)
+        ev[i][1].record()
+    sync_all()
     ms = sum(a.elapsed_time(b) for a, b in ev) / K
     # ---- end to end: pinned host -> device copies and the loss read-back inside the timed region ------
-    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    rays_in, rgbs_in = torch.empty_like(rays_dev), torch.empty_like(rgbs_dev)
-    sync_all()
     t_e2e = 0.0
     for i in range(K):
         flush.zero_()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        rays_in.copy_(rays_host, non_blocking=True)
-        rgbs_in.copy_(rgbs_host, non_blocking=True)
-        loss = step(rays_in, rgbs_in)
+        loss = graphed(rays_host, rgbs_host)          # H2D of rays + targets, then one graph launch
         loss_host = loss.item()                       # device -> host read of the step's result
         t_e2e += time.perf_counter() - t0
     sync_all()
     ms_e2e = t_e2e / K * 1e3
     clocks = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, ms_e2e, ms_eager], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(t[0]), float(t[1])
+    ms, ms_e2e, ms_eager = float(t[0]), float(t[1]), float(t[2])
 
     # ---- roofline: every tensor-core MLP kernel of the step, timed live over the timed region above ------------
     roof = None
@@ -293,9 +303,12 @@ def run_gpu(args):
                     "unit": "GB/s" if hbm else "TFLOP/s",
                     "frac": dom["hbm_frac"] if hbm else dom["tensor_frac"],
                     "peak_source": f"{peaks['src']} (" + ("copy bandwidth" if hbm else "sustained: kernel timed inside the step") + ")",
-                    "ms_per_launch": dom["ms_per_launch"], "share_of_step": dom["ms_per_step"] / ms,
+                    "ms_per_launch": dom["ms_per_launch"], "share_of_step": dom["ms_per_step"] / ms_eager,
                     "traffic": dom["traffic"],
-                    "mlp_kernels_share_of_step": sum(r["ms_per_step"] for r in table) / ms,
+                    "mlp_kernels_share_of_step": sum(r["ms_per_step"] for r in table) / ms_eager,
+                    "timed_in": "an eager pass of the same K steps (per-launch CUDA-event pairs cannot be read back from "
+                                "graph replays); the kernels and their durations are the ones the graph replays",
+                    "eager_ms_per_step": ms_eager,
                     "kernels": table}
         # the same forward kernel without the stash (inference), timed alone: how close the GEMM chain itself gets
         z = torch.sort(torch.rand(B, NC + NF, device=dev) * 4 + 2, -1)[0]
@@ -353,10 +366,12 @@ def run_gpu(args):
                 "config": {"workload": WORKLOAD,
                            "rays_per_gpu": B, "parallelism": f"ray-sharded dp{world}",
                            "l2": "256 MB flush between timed steps; per-step activation traffic >> 126 MB L2",
+                           "launch": "whole step replayed as one CUDA graph (nerf_pl_b200.graph.GraphedStep)",
                            "train_step_flop_per_ray": FLOP_PER_RAY_TRAIN,
                            "step_tensor_roofline_frac": rays_per_s * FLOP_PER_RAY_TRAIN / world / (peaks["bf16_tflops"] * 1e12)},
                 "clocks": clocks, "gpu_launches": launches,
                 "e2e": {"value": world * B / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
+                        "api": "nerf_pl_b200.graph.GraphedStep(step)(rays_host, rgbs_host): the whole step as one CUDA-graph launch",
                         "h2d_bytes_per_step": B * 8 * 4 + B * 3 * 4, "d2h_bytes_per_step": 4},
                 "roofline": roof, "side_rows": side_rows}
         if world == 1 and not args.no_cpu_baseline:
@@ -365,8 +380,10 @@ def run_gpu(args):
                                     "sample": f"1024 rays per call (bounded sample of the 4096-ray batch), median of 5, "
                                               f"{med:.2f} s per call"}
         print(json.dumps(line), flush=True)
+    graphed.close()          # before the process group goes away: the graph holds a captured NCCL all-reduce
     if world > 1:
         dist.barrier()
+        torch.cuda.synchronize()
         dist.destroy_process_group()
 
 

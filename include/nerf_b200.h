@@ -79,6 +79,13 @@ int nrf_mse_pair_bwd(const float* pred_a, const float* pred_b, const float* targ
  * are doubles, rounded to fp32 the way torch rounds its Python scalars (beta and 1 - beta separately). */
 int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr, double beta1,
                   double beta2, double eps, double weight_decay, int64_t step, nrf_stream_t stream);
+/* The same step with the optimizer state on the device, for CUDA-graph replays (a host step count would be baked into
+ * the graph).  `state` = nrf_adam_state_bytes() bytes, 8-byte aligned: { int64 step (starts at 0); double lr; 2 floats
+ * of scratch }.  Each call advances `step` by one on the device and reads `lr` from there; the host writes `lr` (offset 8)
+ * whenever a scheduler changes it. */
+size_t nrf_adam_state_bytes(void);
+int nrf_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double beta1,
+                      double beta2, double eps, double weight_decay, void* state, nrf_stream_t stream);
 
 /* a4  stratified depth sampling — models/rendering.py:216-232
  * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);

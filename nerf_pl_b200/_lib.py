@@ -40,6 +40,8 @@ SIGNATURES = {
     "nrf_mse_pair": (I, [P, P, P, P, L, P, P, P]),
     "nrf_mse_pair_bwd": (I, [P, P, P, L, P, P, P, P]),
     "nrf_adam_step": (I, [P, P, P, P, L, D, D, D, D, D, L, P]),
+    "nrf_adam_state_bytes": (Z, []),
+    "nrf_adam_step_dev": (I, [P, P, P, P, L, D, D, D, D, P, P]),
     "nrf_sample_coarse": (I, [P, P, L, I, I, F, P, P, P]),
     "nrf_embed_fwd": (I, [P, L, I, P, I, P, P]),
     "nrf_embed_bwd": (I, [P, P, L, I, P, I, P, P]),

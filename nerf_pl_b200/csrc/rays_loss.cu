@@ -211,8 +211,24 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
   p = p - k.step_size * (m / denom);                                     // param.addcdiv_(exp_avg, denom, value=-step_size)
 }
 
+// Device-resident optimizer state for CUDA-graph replays (the host's step count would be baked into the graph):
+// state = { int64 step; double lr; float step_size; float bc2_sqrt }.  One thread advances it ahead of the update.
+struct AdamState {
+  long long step;
+  double lr;
+  float step_size, bc2_sqrt;
+};
+
+__global__ void adam_tick_kernel(AdamState* st, double beta1, double beta2) {
+  const long long t = ++st->step;
+  st->step_size = (float)(st->lr / (1.0 - pow(beta1, (double)t)));
+  st->bc2_sqrt = (float)sqrt(1.0 - pow(beta2, (double)t));
+}
+
 __global__ void __launch_bounds__(256) adam_step_kernel(float* __restrict__ p, const float* __restrict__ g,
-                                                        float* __restrict__ m, float* __restrict__ v, int64_t n, AdamK k) {
+                                                        float* __restrict__ m, float* __restrict__ v, int64_t n, AdamK k,
+                                                        const AdamState* __restrict__ st) {
+  if (st) { k.step_size = st->step_size; k.bc2_sqrt = st->bc2_sqrt; }
   const int64_t n4 = n >> 2;
   const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = tid; i < n4; i += nth) {                              // 16-byte lanes: 4 loads in flight per thread
@@ -230,11 +246,26 @@ __global__ void __launch_bounds__(256) adam_step_kernel(float* __restrict__ p, c
 }
 
 __global__ void __launch_bounds__(256) adam_step_scalar_kernel(float* __restrict__ p, const float* __restrict__ g,
-                                                               float* __restrict__ m, float* __restrict__ v, int64_t n, AdamK k) {
+                                                               float* __restrict__ m, float* __restrict__ v, int64_t n, AdamK k,
+                                                               const AdamState* __restrict__ st) {
+  if (st) { k.step_size = st->step_size; k.bc2_sqrt = st->bc2_sqrt; }
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     adam_one(p[i], g[i], m[i], v[i], k);
 }
 }  // namespace nrf
+
+static int adam_launch(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, nrf::AdamK k,
+                       const nrf::AdamState* st, cudaStream_t stream) {
+  const int threads = 256;
+  const bool vec = ((reinterpret_cast<uintptr_t>(param) | reinterpret_cast<uintptr_t>(grad) |
+                     reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0;
+  const int64_t want = ((vec ? (n + 3) / 4 : n) + threads - 1) / threads;
+  const int blocks = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
+  if (vec) nrf::adam_step_kernel<<<blocks, threads, 0, stream>>>(param, grad, exp_avg, exp_avg_sq, n, k, st);
+  else nrf::adam_step_scalar_kernel<<<blocks, threads, 0, stream>>>(param, grad, exp_avg, exp_avg_sq, n, k, st);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
 
 extern "C" int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr,
                              double beta1, double beta2, double eps, double weight_decay, int64_t step,
@@ -242,23 +273,36 @@ extern "C" int nrf_adam_step(float* param, const float* grad, float* exp_avg, fl
   NRF_REQUIRE(n >= 0 && step >= 1, "nrf_adam_step: bad size or step");
   if (n == 0) return NRF_OK;
   NRF_REQUIRE(param && grad && exp_avg && exp_avg_sq, "nrf_adam_step: null pointer");
-  const double bc1 = 1.0 - std::pow(beta1, (double)step);
-  const double bc2 = 1.0 - std::pow(beta2, (double)step);
   nrf::AdamK k;
-  k.step_size = (float)(lr / bc1);
+  k.step_size = (float)(lr / (1.0 - std::pow(beta1, (double)step)));
   k.beta2 = (float)beta2;
   k.eps = (float)eps;
   k.weight_decay = (float)weight_decay;
   k.w1 = (float)(1.0 - beta1);
   k.w2 = (float)(1.0 - beta2);
-  k.bc2_sqrt = (float)std::sqrt(bc2);
-  const int threads = 256;
-  const bool vec = ((reinterpret_cast<uintptr_t>(param) | reinterpret_cast<uintptr_t>(grad) |
-                     reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0;
-  const int64_t want = ((vec ? (n + 3) / 4 : n) + threads - 1) / threads;
-  const int blocks = (int)(want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8);
-  if (vec) nrf::adam_step_kernel<<<blocks, threads, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, k);
-  else nrf::adam_step_scalar_kernel<<<blocks, threads, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, k);
+  k.bc2_sqrt = (float)std::sqrt(1.0 - std::pow(beta2, (double)step));
+  return adam_launch(param, grad, exp_avg, exp_avg_sq, n, k, nullptr, as_stream(stream));
+}
+
+extern "C" size_t nrf_adam_state_bytes(void) { return sizeof(nrf::AdamState); }
+
+extern "C" int nrf_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
+                                 double beta1, double beta2, double eps, double weight_decay, void* state,
+                                 nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0, "nrf_adam_step_dev: bad size");
+  NRF_REQUIRE(state && (reinterpret_cast<uintptr_t>(state) & 7) == 0, "nrf_adam_step_dev: state must be 8-byte aligned");
+  NRF_REQUIRE(n == 0 || (param && grad && exp_avg && exp_avg_sq), "nrf_adam_step_dev: null pointer");
+  nrf::AdamState* st = static_cast<nrf::AdamState*>(state);
+  nrf::adam_tick_kernel<<<1, 1, 0, as_stream(stream)>>>(st, beta1, beta2);
   NRF_LAUNCH_CHECK();
-  return NRF_OK;
+  if (n == 0) return NRF_OK;
+  nrf::AdamK k;
+  k.step_size = 0.f;
+  k.bc2_sqrt = 1.f;
+  k.beta2 = (float)beta2;
+  k.eps = (float)eps;
+  k.weight_decay = (float)weight_decay;
+  k.w1 = (float)(1.0 - beta1);
+  k.w2 = (float)(1.0 - beta2);
+  return adam_launch(param, grad, exp_avg, exp_avg_sq, n, k, st, as_stream(stream));
 }

@@ -18,8 +18,15 @@ from ..mlp import RenderPass
 
 
 def _is_pow2_bands(emb):
+    # checked once per (buffer, version): a device-resident freq_bands would cost a host sync per render otherwise
+    # (and a sync is illegal while a CUDA graph is being captured)
     fb = emb.freq_bands
-    return bool(torch.equal(fb.cpu().float(), 2.0 ** torch.arange(emb.N_freqs, dtype=torch.float32)))
+    tag = (fb.data_ptr(), fb._version, int(emb.N_freqs))
+    cache = emb.__dict__.get("_nrf_pow2")
+    if cache is None or cache[0] != tag:
+        ok = bool(torch.equal(fb.cpu().float(), 2.0 ** torch.arange(emb.N_freqs, dtype=torch.float32)))
+        emb.__dict__["_nrf_pow2"] = cache = (tag, ok)
+    return cache[1]
 
 
 def _model_cfg(model, embeddings, sigma_only, white_back, noise_std):

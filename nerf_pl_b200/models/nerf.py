@@ -68,7 +68,10 @@ class NeRF(nn.Module):
         params = self.ordered_parameters()
         tag = tuple((p.data_ptr(), p._version) for p in params)
         cache = self.__dict__.get("_nrf_pack")
-        if cache is None or cache[0] != tag or cache[1].device != params[0].device:
+        # while a CUDA graph is being captured the re-pack is always recorded: replays run no host code, so the
+        # version check above cannot see the captured optimizer step
+        capturing = params[0].is_cuda and torch.cuda.is_current_stream_capturing()
+        if cache is None or cache[0] != tag or cache[1].device != params[0].device or capturing:
             buf = cache[1] if cache is not None and cache[1].device == params[0].device else None
             with torch.no_grad():
                 buf = _mlp.pack_weights(self._spec, [p.detach() for p in params], buf)

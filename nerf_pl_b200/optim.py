@@ -13,7 +13,8 @@ from .ops import _p, _stream
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, bucket=None):
+    def __init__(self, modules, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, bucket=None,
+                 capturable=False):
         modules = list(modules)
         self.bucket = bucket if bucket is not None else GradBucket(modules)
         params = self.bucket.params
@@ -31,6 +32,12 @@ class FusedAdam(torch.optim.Optimizer):
         self.exp_avg = torch.zeros_like(self.flat_param)
         self.exp_avg_sq = torch.zeros_like(self.flat_param)
         self._steps = 0
+        # capturable: step count and lr live on the device so a captured step (graph.GraphedStep) replays correctly
+        self._state = None
+        if capturable:
+            assert _lib.load().nrf_adam_state_bytes() == 24
+            self._state = torch.zeros(3, dtype=torch.int64, device=self.flat_param.device)   # {step, lr (f64), scratch}
+            self._state_lr = None
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
 
     def zero_grad(self, set_to_none=False):
@@ -42,21 +49,41 @@ class FusedAdam(torch.optim.Optimizer):
         g = self.param_groups[0]
         self._steps += 1
         with torch.cuda.device(self.flat_param.device):
-            _lib.call("nrf_adam_step", _p(self.flat_param), _p(self.bucket.flat), _p(self.exp_avg), _p(self.exp_avg_sq),
-                      self.flat_param.numel(), float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
-                      float(g["weight_decay"]), self._steps, _stream())
+            if self._state is not None:
+                if not torch.cuda.is_current_stream_capturing():
+                    self.sync_lr()
+                _lib.call("nrf_adam_step_dev", _p(self.flat_param), _p(self.bucket.flat), _p(self.exp_avg),
+                          _p(self.exp_avg_sq), self.flat_param.numel(), float(g["betas"][0]), float(g["betas"][1]),
+                          float(g["eps"]), float(g["weight_decay"]), _p(self._state), _stream())
+            else:
+                _lib.call("nrf_adam_step", _p(self.flat_param), _p(self.bucket.flat), _p(self.exp_avg),
+                          _p(self.exp_avg_sq), self.flat_param.numel(), float(g["lr"]), float(g["betas"][0]),
+                          float(g["betas"][1]), float(g["eps"]), float(g["weight_decay"]), self._steps, _stream())
         # parameter version counters drive the weight re-pack cache (NeRF.packed_weights); the kernel wrote through
         # the flat buffer, so bump them here (one C++ call, no launches)
         torch.autograd.graph.increment_version(self.bucket.params)
         return loss
 
+    def sync_lr(self):
+        """capturable mode: push param_groups[0]['lr'] to the device if a scheduler changed it (call before a replay)."""
+        lr = float(self.param_groups[0]["lr"])
+        if self._state is not None and lr != self._state_lr:
+            self._state[1:2].view(torch.float64).copy_(torch.tensor([lr], dtype=torch.float64))
+            self._state_lr = lr
+
+    @property
+    def steps(self):
+        return int(self._state[0].item()) if self._state is not None else self._steps
+
     def state_dict(self):
-        return {"steps": self._steps, "flat_param": self.flat_param, "exp_avg": self.exp_avg,
+        return {"steps": self.steps, "flat_param": self.flat_param, "exp_avg": self.exp_avg,
                 "exp_avg_sq": self.exp_avg_sq, "param_groups": [{k: v for k, v in g.items() if k != "params"}
                                                                   for g in self.param_groups]}
 
     def load_state_dict(self, sd):
         self._steps = int(sd["steps"])
+        if self._state is not None:
+            self._state[0:1].fill_(self._steps)
         with torch.no_grad():
             self.flat_param.copy_(sd["flat_param"])
             self.exp_avg.copy_(sd["exp_avg"])

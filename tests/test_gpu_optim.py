@@ -105,3 +105,84 @@ def test_fused_adam_trains_like_torch_adam(dev):
     opt_a.bucket.flat.fill_(1.0)
     opt_a.step()
     assert not torch.equal(before, a[0].packed_weights())
+
+
+def test_adam_device_state_matches_host_steps(dev):
+    """nrf_adam_step_dev (step count and lr on the device, for graph replays) == nrf_adam_step with host counters."""
+    from nerf_pl_b200 import _lib
+    from nerf_pl_b200.ops import _p, _stream
+    g = torch.Generator().manual_seed(21)
+    n = 1027
+    p0 = torch.randn(n, generator=g)
+    pa, pb = p0.to(dev), p0.to(dev)
+    ma, va, mb, vb = (torch.zeros(n, device=dev) for _ in range(4))
+    state = torch.zeros(3, dtype=torch.int64, device=dev)
+    state[1:2].view(torch.float64).copy_(torch.tensor([1e-3], dtype=torch.float64))
+    for t in range(1, 6):
+        gr = torch.randn(n, generator=g).to(dev)
+        if t == 4:                                   # a scheduler drops the learning rate
+            state[1:2].view(torch.float64).copy_(torch.tensor([1e-4], dtype=torch.float64))
+        lr = 1e-3 if t < 4 else 1e-4
+        _lib.call("nrf_adam_step", _p(pa), _p(gr), _p(ma), _p(va), n, lr, 0.9, 0.999, 1e-8, 1e-5, t, _stream())
+        _lib.call("nrf_adam_step_dev", _p(pb), _p(gr), _p(mb), _p(vb), n, 0.9, 0.999, 1e-8, 1e-5, _p(state), _stream())
+        assert torch.equal(pa, pb) and torch.equal(ma, mb) and torch.equal(va, vb), t
+    assert int(state[0].item()) == 5
+
+
+def test_graphed_step_matches_eager(dev):
+    """graph.GraphedStep: a captured training step (render, loss, backward, Adam, re-pack) replayed 4 times against the
+    same steps run eagerly on a twin; deterministic sampling (perturb = 0, noise_std = 0) so both arms see the same
+    numbers.  fp32 atomics order the gradient sums differently run to run, hence Adam-update-sized tolerances."""
+    import copy
+    from nerf_pl_b200.graph import GraphedStep
+    from nerf_pl_b200.losses import loss_dict
+    from nerf_pl_b200.models.nerf import Embedding, NeRF
+    from nerf_pl_b200.models.rendering import render_rays
+    from nerf_pl_b200.optim import FusedAdam
+    torch.manual_seed(4)
+    emb = [Embedding(3, 10), Embedding(3, 4)]
+    a = [NeRF().to(dev), NeRF().to(dev)]
+    b = copy.deepcopy(a)
+    loss_fn = loss_dict["mse"]()
+
+    def make_step(models, opt):
+        def step(rays, rgbs):
+            opt.zero_grad()
+            res = render_rays(models, emb, rays, N_samples=32, N_importance=32, perturb=0, noise_std=0, chunk=1 << 15)
+            loss = loss_fn(res, rgbs)
+            loss.backward()
+            opt.step()
+            return loss
+        return step
+
+    opt_a = FusedAdam(a, lr=5e-4, capturable=True)
+    opt_b = FusedAdam(b, lr=5e-4)
+    g = torch.Generator().manual_seed(10)
+
+    def batch():
+        o = torch.randn(256, 3, generator=g) * 0.3
+        d = torch.nn.functional.normalize(torch.randn(256, 3, generator=g), dim=-1)
+        rays = torch.cat([o, d, torch.full((256, 1), 2.0), torch.full((256, 1), 6.0)], 1)
+        return rays.pin_memory(), torch.rand(256, 3, generator=g).pin_memory()
+
+    r0, c0 = batch()
+    step_b = make_step(b, opt_b)
+    graphed = GraphedStep(make_step(a, opt_a), (r0.to(dev), c0.to(dev)), warmup=3, optimizers=[opt_a])
+    for _ in range(3):                       # the graphed arm's warm-up really trained on the example batch
+        step_b(r0.to(dev), c0.to(dev))
+    for it in range(4):
+        r, c = batch()
+        la = graphed(r, c).item()            # host-pinned inputs: the H2D copies are part of the call
+        lb = step_b(r.to(dev), c.to(dev)).item()
+        assert abs(la - lb) <= 5e-3 * abs(lb) + 1e-6, (it, la, lb)
+    assert opt_a.steps == 7 and graphed.replays == 4
+    for ma, mb in zip(a, b):
+        for (na, pa), (_, pb) in zip(ma.named_parameters(), mb.named_parameters()):
+            assert (pa - pb).abs().max().item() <= 7 * 5e-4 + 1e-7, na
+            assert ((pa - pb).abs() <= 5e-5).float().mean().item() > 0.9, na
+    # the replayed re-pack follows the replayed optimizer step: an eager render after the replays sees current weights
+    with torch.no_grad():
+        r, c = batch()
+        ra = render_rays(a, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
+        rb = render_rays(b, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
+    assert (ra["rgb_fine"] - rb["rgb_fine"]).abs().max().item() < 2e-2
