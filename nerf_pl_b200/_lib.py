@@ -63,6 +63,12 @@ SIGNATURES = {
     "nrf_shadow_workspace_bytes": (Z, [L, L]),
     "nrf_shadow_fwd": (I, [P, P, P, P, P, P, P, P, P, L, I, I, I, F, F, F, F, I, F, P, P, Z, P]),
     "nrf_normed_w": (I, [P, P, P, P, L, P, P]),
+    "nrf_project_to_light": (I, [P, P, P, P, L, P, P, L, I, P, P, P, P]),
+    "nrf_shadow_map_workspace_bytes": (Z, []),
+    "nrf_shadow_map_fwd": (I, [P, P, L, I, F, F, F, F, I, I, P, P, P]),
+    "nrf_shadow_map_bwd": (I, [P, P, L, I, F, F, F, F, I, I, P, P, P, P]),
+    "nrf_light_gather": (I, [P, P, L, I, I, P, P, P]),
+    "nrf_light_scatter": (I, [P, P, L, L, P, P]),
     "nrf_dbg_set_counters": (None, [P]),
     "nrf_dbg_mma_rate": (I, [I, I, P, P]),
     "nrf_dbg_store_rate": (I, [P, ctypes.c_uint64, c_uint32, I, I, I, P, P]),

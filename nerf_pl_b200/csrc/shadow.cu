@@ -99,9 +99,11 @@ __global__ void segment_kernel(const float* __restrict__ eye, int64_t n, int* __
                 eye[i * 3 + 2] != eye[(i - 1) * 3 + 2];
       }
       v = start ? (int)i : 0;
-      seg_min[i] = float_key(FLT_MAX);
-      seg_max[i] = float_key(-FLT_MAX);
-      s1[i] = 0.f; s2[i] = 0.f; cnt_min[i] = 0; cnt_max[i] = 0;
+      if (seg_min) {
+        seg_min[i] = float_key(FLT_MAX);
+        seg_max[i] = float_key(-FLT_MAX);
+        s1[i] = 0.f; s2[i] = 0.f; cnt_min[i] = 0; cnt_max[i] = 0;
+      }
     }
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -389,6 +391,292 @@ extern "C" int nrf_normed_w(const float* pixel_depth, const float* value, const 
   if (n == 0) return NRF_OK;
   NRF_REQUIRE(pixel_depth && value && passthrough && M && out, "nrf_normed_w: null pointer");
   normed_w_kernel<<<sgrid(n), 256, 0, as_stream(stream)>>>(pixel_depth, value, passthrough, M, n, out);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+
+// ---- §8f rank 2: the pieces the light-sampler trainer calls one by one (train_light_sampler.py:141-196) -----------------
+// a24 get_K / get_projections / get_diff_projections (rendering_shadows.py:484-546, efficient_shadow_mapping.py:13-17,
+//     :65-83): K = [ul, vl, wl] per camera ray, cameras per ray (segmented by eye_pos like the reference's loop) or one
+//     camera for the whole batch; `normalised` = the depth column already is w (get_diff_projections).
+// a25 generate_shadow_map / normalize_min_max (:10-11, :103-130) on explicit (wl, w_light_bounded) vectors: whole-vector
+//     min/max, warp-reduced before the atomics.
+// a26 get_projected_depths (:85-100): clamp, truncate, gather from the light map; backward scatters.
+namespace nrf {
+
+struct ProjCam {
+  float R[9], Q[3], nrm;
+};
+
+__device__ __forceinline__ ProjCam proj_setup(const float* __restrict__ M, const float* __restrict__ eye,
+                                              const float* __restrict__ light_Minv, const float* __restrict__ light_eye,
+                                              float a, float b, float c, int normalised) {
+  ProjCam pc;
+  const float cx = mat_row_dot(M, 0, a, b, c), cy = mat_row_dot(M, 1, a, b, c), cz = mat_row_dot(M, 2, a, b, c);
+  pc.nrm = normalised ? 1.0f : sqrtf(cx * cx + cy * cy + cz * cz) + kShadowEps;
+  const float ex = eye[0] - light_eye[0], ey = eye[1] - light_eye[1], ez = eye[2] - light_eye[2];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float l0 = light_Minv[r * 3], l1 = light_Minv[r * 3 + 1], l2 = light_Minv[r * 3 + 2];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) pc.R[r * 3 + q] = (l0 * M[q] + l1 * M[3 + q]) + l2 * M[6 + q];
+    pc.Q[r] = (l0 * ex + l1 * ey) + l2 * ez;
+  }
+  return pc;
+}
+
+// g_K == nullptr: forward, out = K (n,3).  Otherwise backward: out = g_depth (n).
+__global__ void project_to_light_kernel(const float* __restrict__ cam_pixels, const float* __restrict__ cam_depth,
+                                        const float* __restrict__ cam_M, const float* __restrict__ cam_eye,
+                                        const int* __restrict__ seg_start, const float* __restrict__ light_Minv,
+                                        const float* __restrict__ light_eye, int64_t n, int normalised,
+                                        const float* __restrict__ g_K, float* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t s = seg_start ? seg_start[i] : 0;
+    const float a = cam_pixels[i * 3], b = cam_pixels[i * 3 + 1], c = cam_pixels[i * 3 + 2];
+    const ProjCam pc = proj_setup(cam_M + s * 9, cam_eye + s * 3, light_Minv, light_eye, a, b, c, normalised);
+    const float wc = cam_depth[i] / pc.nrm;
+    const float p0 = mat_row_dot(pc.R, 0, a, b, c), p1 = mat_row_dot(pc.R, 1, a, b, c), p2 = mat_row_dot(pc.R, 2, a, b, c);
+    const float u = wc * p0 + pc.Q[0], v = wc * p1 + pc.Q[1], wl = wc * p2 + pc.Q[2];
+    if (!g_K) {
+      out[i * 3] = u / wl; out[i * 3 + 1] = v / wl; out[i * 3 + 2] = wl;
+    } else {
+      // d(u/wl)/dwc = p0/wl - u p2/wl^2, same for v; dwl/dwc = p2; dwc/ddepth = 1/nrm
+      const float inv = 1.0f / wl;
+      const float g_wc = g_K[i * 3] * (p0 - u * inv * p2) * inv + g_K[i * 3 + 1] * (p1 - v * inv * p2) * inv +
+                         g_K[i * 3 + 2] * p2;
+      out[i] = g_wc / pc.nrm;
+    }
+  }
+}
+
+// ---- a25: [0] min key, [1] max key, then float s1, s2, int cnt_min, cnt_max
+struct MapWs {
+  int* keys;
+  float* sums;
+  int* cnt;
+};
+
+__global__ void map_init_kernel(MapWs w) {
+  w.keys[0] = float_key(FLT_MAX); w.keys[1] = float_key(-FLT_MAX);
+  w.sums[0] = 0.f; w.sums[1] = 0.f; w.cnt[0] = 0; w.cnt[1] = 0;
+}
+
+__device__ __forceinline__ float map_diff(const float* __restrict__ wl, const float* __restrict__ wlb, int64_t i) {
+  return wlb ? wl[i] - wlb[i] : wl[i];
+}
+
+__global__ void map_minmax_kernel(const float* __restrict__ wl, const float* __restrict__ wlb, int64_t n, MapWs w) {
+  int mn = float_key(FLT_MAX), mx = float_key(-FLT_MAX);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = float_key(map_diff(wl, wlb, i));
+    mn = min(mn, k); mx = max(mx, k);
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMin(w.keys, mn); atomicMax(w.keys + 1, mx); }
+}
+
+__global__ void map_shade_kernel(const float* __restrict__ wl, const float* __restrict__ wlb, int64_t n, MapWs w,
+                                 ShadowCfg cfg, int stack_clip, float* __restrict__ out) {
+  float mn = 0.f, mx = 0.f;
+  if (cfg.mode == 2) { mn = key_float(w.keys[0]); mx = key_float(w.keys[1]); }
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float v = shadow_value(map_diff(wl, wlb, i), mn, mx, cfg);
+    if (stack_clip) {
+      v = fminf(fmaxf(v, 0.f), 1.f);
+      out[i * 3] = v; out[i * 3 + 1] = v; out[i * 3 + 2] = v;
+    } else {
+      out[i] = v;
+    }
+  }
+}
+
+__device__ __forceinline__ float map_upstream(const float* __restrict__ g_out, int64_t i, float d, float mn, float mx,
+                                              const ShadowCfg& cfg, int stack_clip) {
+  if (stack_clip) return upstream(g_out, i, d, mn, mx, cfg);
+  float gy = g_out[i];                                            // normalize_min_max alone: no clip, no stack
+  if (cfg.mode == 1) {
+    const float a = d / cfg.delta;
+    return gy * (a > cfg.epsilon ? 1.f : (a == cfg.epsilon ? 0.5f : 0.f)) / cfg.delta;
+  }
+  if (cfg.sigmoid) { const float v = shadow_value(d, mn, mx, cfg); gy *= v * (1.f - v); }
+  return gy * (cfg.new_max - cfg.new_min);
+}
+
+__global__ void map_bwd_reduce_kernel(const float* __restrict__ g_out, const float* __restrict__ wl,
+                                      const float* __restrict__ wlb, int64_t n, MapWs w, ShadowCfg cfg, int stack_clip) {
+  const float mn = key_float(w.keys[0]), mx = key_float(w.keys[1]);
+  float s1 = 0.f, s2 = 0.f;
+  int c0 = 0, c1 = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float d = map_diff(wl, wlb, i);
+    const float gy = map_upstream(g_out, i, d, mn, mx, cfg, stack_clip);
+    s1 += gy; s2 += gy * (d - mn);
+    c0 += d == mn; c1 += d == mx;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    c0 += __shfl_xor_sync(0xffffffffu, c0, o); c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(w.sums, s1); atomicAdd(w.sums + 1, s2);
+    if (c0) atomicAdd(w.cnt, c0);
+    if (c1) atomicAdd(w.cnt + 1, c1);
+  }
+}
+
+__global__ void map_bwd_apply_kernel(const float* __restrict__ g_out, const float* __restrict__ wl,
+                                     const float* __restrict__ wlb, int64_t n, MapWs w, ShadowCfg cfg, int stack_clip,
+                                     float* __restrict__ g_diff) {
+  float mn = 0.f, mx = 0.f, D = 1.f, g_mn = 0.f, g_mx = 0.f;
+  if (cfg.mode == 2) {
+    mn = key_float(w.keys[0]); mx = key_float(w.keys[1]);
+    D = mx - mn + kShadowEps;
+    g_mn = (-w.sums[0] / D + w.sums[1] / (D * D)) / (float)max(w.cnt[0], 1);   // through tensor.min()
+    g_mx = (-w.sums[1] / (D * D)) / (float)max(w.cnt[1], 1);                    // through tensor.max()
+  }
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float d = map_diff(wl, wlb, i);
+    float gd = map_upstream(g_out, i, d, mn, mx, cfg, stack_clip);
+    if (cfg.mode == 2) {
+      gd /= D;
+      if (d == mn) gd += g_mn;
+      if (d == mx) gd += g_mx;
+    }
+    g_diff[i] = gd;
+  }
+}
+
+// ---- a26
+__global__ void light_gather_kernel(const float* __restrict__ K, const float* __restrict__ w_light, int64_t n, int res_w,
+                                    int res_h, float* __restrict__ wlb, int* __restrict__ gidx) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float ul = fminf(fmaxf(K[i * 3], 0.f), (float)res_w - 1.0f);
+    const float vl = fminf(fmaxf(K[i * 3 + 1], 0.f), (float)res_h - 1.0f);
+    const int gi = (int)vl * res_h + (int)ul;          // w_light.view(w,h)[vl, ul]  (:98)
+    gidx[i] = gi;
+    wlb[i] = w_light[gi];
+  }
+}
+
+__global__ void light_scatter_kernel(const float* __restrict__ g_wlb, const int* __restrict__ gidx, int64_t n,
+                                     float* __restrict__ g_wlight) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    atomicAdd(g_wlight + gidx[i], g_wlb[i]);
+}
+
+static MapWs map_carve(void* ws) {
+  MapWs w;
+  w.keys = static_cast<int*>(ws);
+  w.sums = reinterpret_cast<float*>(w.keys + 2);
+  w.cnt = w.keys + 4;
+  return w;
+}
+}  // namespace nrf
+
+extern "C" int nrf_project_to_light(const float* cam_pixels, const float* cam_depth, const float* cam_M,
+                                    const float* cam_eye, int64_t n_cam, const float* light_Minv, const float* light_eye,
+                                    int64_t n, int normalised, const float* g_K, float* out, int* seg_ws,
+                                    nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0 && n < (int64_t)1 << 31, "nrf_project_to_light: bad size");
+  NRF_REQUIRE(n_cam == 1 || n_cam == n, "nrf_project_to_light: %lld cameras for %lld rays (1 or one per ray)",
+              (long long)n_cam, (long long)n);
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(cam_pixels && cam_depth && cam_M && cam_eye && light_Minv && light_eye && out,
+              "nrf_project_to_light: null pointer");
+  cudaStream_t st = as_stream(stream);
+  const int* seg = nullptr;
+  if (n_cam != 1) {
+    NRF_REQUIRE(seg_ws != nullptr, "nrf_project_to_light: per-ray cameras need a workspace of n ints");
+    segment_kernel<<<1, 1024, 0, st>>>(cam_eye, n, seg_ws, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+    NRF_LAUNCH_CHECK();
+    seg = seg_ws;
+  }
+  project_to_light_kernel<<<sgrid(n), 256, 0, st>>>(cam_pixels, cam_depth, cam_M, cam_eye, seg, light_Minv, light_eye, n,
+                                                    normalised, g_K, out);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" size_t nrf_shadow_map_workspace_bytes(void) { return 32; }
+
+static int map_check(const char* who, const float* wl, int64_t n, int mode, void* ws) {
+  NRF_REQUIRE(n >= 0, "%s: bad size", who);
+  NRF_REQUIRE(mode == 1 || mode == 2, "%s: shadow mode %d not found", who, mode);
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(wl && ws, "%s: null pointer", who);
+  return NRF_OK;
+}
+
+extern "C" int nrf_shadow_map_fwd(const float* wl, const float* w_light_bounded, int64_t n, int mode, float delta,
+                                  float epsilon, float new_min, float new_max, int sigmoid, int stack_clip, float* out,
+                                  void* workspace, nrf_stream_t stream) {
+  int rc = map_check("nrf_shadow_map_fwd", wl, n, mode, workspace);
+  if (rc || n == 0) return rc;
+  NRF_REQUIRE(out != nullptr, "nrf_shadow_map_fwd: null output");
+  cudaStream_t st = as_stream(stream);
+  const MapWs w = map_carve(workspace);
+  const ShadowCfg cfg{mode, sigmoid, delta, epsilon, new_min, new_max, 0.f};
+  if (mode == 2) {
+    map_init_kernel<<<1, 1, 0, st>>>(w);
+    NRF_LAUNCH_CHECK();
+    map_minmax_kernel<<<sgrid(n), 256, 0, st>>>(wl, w_light_bounded, n, w);
+    NRF_LAUNCH_CHECK();
+  }
+  map_shade_kernel<<<sgrid(n), 256, 0, st>>>(wl, w_light_bounded, n, w, cfg, stack_clip, out);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" int nrf_shadow_map_bwd(const float* wl, const float* w_light_bounded, int64_t n, int mode, float delta,
+                                  float epsilon, float new_min, float new_max, int sigmoid, int stack_clip,
+                                  const float* g_out, float* g_diff, void* workspace, nrf_stream_t stream) {
+  int rc = map_check("nrf_shadow_map_bwd", wl, n, mode, workspace);
+  if (rc || n == 0) return rc;
+  NRF_REQUIRE(g_out && g_diff, "nrf_shadow_map_bwd: null pointer");
+  cudaStream_t st = as_stream(stream);
+  const MapWs w = map_carve(workspace);
+  const ShadowCfg cfg{mode, sigmoid, delta, epsilon, new_min, new_max, 0.f};
+  if (mode == 2) {
+    map_init_kernel<<<1, 1, 0, st>>>(w);
+    NRF_LAUNCH_CHECK();
+    map_minmax_kernel<<<sgrid(n), 256, 0, st>>>(wl, w_light_bounded, n, w);
+    NRF_LAUNCH_CHECK();
+    map_bwd_reduce_kernel<<<sgrid(n), 256, 0, st>>>(g_out, wl, w_light_bounded, n, w, cfg, stack_clip);
+    NRF_LAUNCH_CHECK();
+  }
+  map_bwd_apply_kernel<<<sgrid(n), 256, 0, st>>>(g_out, wl, w_light_bounded, n, w, cfg, stack_clip, g_diff);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" int nrf_light_gather(const float* K, const float* w_light, int64_t n, int res_w, int res_h,
+                                float* w_light_bounded, int* gidx, nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0 && res_w >= 1 && res_h >= 1, "nrf_light_gather: bad sizes");
+  NRF_REQUIRE(res_w == res_h, "nrf_light_gather: only square light maps are supported, like the reference "
+              "(efficient_shadow_mapping.py:3-4), got %dx%d", res_w, res_h);
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(K && w_light && w_light_bounded && gidx, "nrf_light_gather: null pointer");
+  light_gather_kernel<<<sgrid(n), 256, 0, as_stream(stream)>>>(K, w_light, n, res_w, res_h, w_light_bounded, gidx);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" int nrf_light_scatter(const float* g_wlb, const int* gidx, int64_t n, int64_t n_light, float* g_wlight,
+                                 nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0 && n_light >= 0, "nrf_light_scatter: bad sizes");
+  if (n_light == 0) return NRF_OK;
+  NRF_REQUIRE(g_wlight != nullptr, "nrf_light_scatter: null output");
+  NRF_CUDA(cudaMemsetAsync(g_wlight, 0, (size_t)n_light * sizeof(float), as_stream(stream)));
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(g_wlb && gidx, "nrf_light_scatter: null pointer");
+  light_scatter_kernel<<<sgrid(n), 256, 0, as_stream(stream)>>>(g_wlb, gidx, n, g_wlight);
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

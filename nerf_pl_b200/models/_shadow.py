@@ -31,9 +31,11 @@ class ShadowTest(torch.autograd.Function):
         nb = lib.nrf_shadow_workspace_bytes(n, w * h)
         ws = torch.empty(nb, dtype=torch.uint8, device=cam_depth.device)
         out = torch.empty(n, 3, device=cam_depth.device)
+        # new_min / new_max are accepted and ignored: the reference's generate_shadow_map calls normalize_min_max(diff)
+        # without forwarding them (efficient_shadow_mapping.py:124), so the range always is [0, 1]
         args = (_p(cam_pixels), _p(cam_depth), _p(cam_M), _p(cam_eye), _p(light_Minv), _p(light_M), _p(light_eye),
                 _p(light_pixels), _p(light_depth), n, w, h, _MODES[mode], float(delta), float(epsilon),
-                float(new_min), float(new_max), int(bool(sigmoid)))
+                0.0, 1.0, int(bool(sigmoid)))
         _lib.call("nrf_shadow_fwd", *args, float(out_bias), _p(out), _p(ws), nb, _stream())
         ctx.args, ctx.static, ctx.nb = args, static, nb
         ctx.save_for_backward(cam_depth, light_depth)
@@ -89,6 +91,120 @@ def efficient_sm_impl(prefix, cam_pixels, light_pixels, cam_results, light_resul
     return cam_results
 
 
+class ProjectToLight(torch.autograd.Function):
+    """K (n,3) = [ul, vl, wl] of camera rays in the light's image (a24: efficient_shadow_mapping.py:13-17, :65-83 and the
+    per-ray-camera loop of rendering_shadows.py:484-546).  cam_M (n_cam,3,3), cam_eye (n_cam,3) with n_cam = n or 1.
+    Differentiable w.r.t. the depth / w vector."""
+
+    @staticmethod
+    def forward(ctx, depth, cam_pixels, cam_M, cam_eye, light_Minv, light_eye, normalised):
+        depth = _dev(depth, "depth").reshape(-1)
+        n = depth.numel()
+        n_cam = cam_M.shape[0]
+        if cam_pixels.shape != (n, 3):
+            raise RuntimeError(f"cam_pixels must be ({n}, 3), got {tuple(cam_pixels.shape)}")
+        seg = torch.empty(n, dtype=torch.int32, device=depth.device) if n_cam != 1 else None
+        out = torch.empty(n, 3, device=depth.device)
+        ctx.args = (_p(cam_pixels), _p(depth), _p(cam_M), _p(cam_eye), n_cam, _p(light_Minv), _p(light_eye), n,
+                    int(bool(normalised)))
+        ctx.keep = (cam_pixels, cam_M, cam_eye, light_Minv, light_eye, seg)
+        ctx.save_for_backward(depth)
+        _lib.call("nrf_project_to_light", *ctx.args, None, _p(out), _p(seg), _stream())
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (depth,) = ctx.saved_tensors
+        g = _dev(g, "grad")
+        gd = torch.empty_like(depth)
+        _lib.call("nrf_project_to_light", *ctx.args, _p(g), _p(gd), _p(ctx.keep[5]), _stream())
+        return (gd,) + (None,) * 6
+
+
+class ShadowMap(torch.autograd.Function):
+    """generate_shadow_map / normalize_min_max on explicit vectors (a25: efficient_shadow_mapping.py:10-11, :103-130).
+    stack_clip: (n,3) stacked and clipped output; otherwise (n,)."""
+
+    @staticmethod
+    def forward(ctx, wl, wlb, mode, delta, epsilon, new_min, new_max, sigmoid, stack_clip):
+        if mode not in _MODES:
+            raise ValueError("{} not found".format(mode))
+        wl = _dev(wl, "wl").reshape(-1)
+        if wlb is not None:
+            wlb = _dev(wlb, "w_light_bounded").reshape(-1)
+            if wlb.numel() != wl.numel():
+                raise RuntimeError("wl and w_light_bounded must have the same number of elements")
+        n = wl.numel()
+        ws = torch.empty(32, dtype=torch.uint8, device=wl.device)
+        out = torch.empty((n, 3) if stack_clip else (n,), device=wl.device)
+        if stack_clip:       # generate_shadow_map ignores new_min / new_max (efficient_shadow_mapping.py:124)
+            new_min, new_max = 0.0, 1.0
+        ctx.args = (_p(wl), _p(wlb), n, _MODES[mode], float(delta), float(epsilon), float(new_min), float(new_max),
+                    int(bool(sigmoid)), int(bool(stack_clip)))
+        ctx.keep = (wl, wlb)
+        ctx.has_b = wlb is not None
+        _lib.call("nrf_shadow_map_fwd", *ctx.args, _p(out), _p(ws), _stream())
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        wl, _ = ctx.keep
+        g = _dev(g, "grad")
+        gd = torch.empty_like(wl)
+        ws = torch.empty(32, dtype=torch.uint8, device=wl.device)
+        _lib.call("nrf_shadow_map_bwd", *ctx.args, _p(g), _p(gd), _p(ws), _stream())
+        return (gd, -gd if ctx.has_b and ctx.needs_input_grad[1] else None) + (None,) * 7
+
+
+class LightGather(torch.autograd.Function):
+    """w_light.view(w,h)[clamp(vl), clamp(ul)] (a26: efficient_shadow_mapping.py:85-100); gradient scatters into w_light
+    (the clamped, truncated indices carry none, as in the reference)."""
+
+    @staticmethod
+    def forward(ctx, K, w_light, res):
+        K, w_light = _dev(K, "K"), _dev(w_light, "w_light").reshape(-1)
+        w, h = int(res[0]), int(res[1])
+        if K.dim() != 2 or K.shape[1] != 3:
+            raise RuntimeError("K must be (num_rays, 3)")
+        if w_light.numel() != w * h:
+            raise RuntimeError(f"light map has {w_light.numel()} texels, expected {w}x{h}")
+        n = K.shape[0]
+        out = torch.empty(n, device=K.device)
+        gidx = torch.empty(n, dtype=torch.int32, device=K.device)
+        _lib.call("nrf_light_gather", _p(K), _p(w_light), n, w, h, _p(out), _p(gidx), _stream())
+        ctx.gidx, ctx.hw = gidx, w * h
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        g = _dev(g, "grad")
+        gl = torch.empty(ctx.hw, device=g.device)
+        _lib.call("nrf_light_scatter", _p(g), _p(ctx.gidx), g.numel(), ctx.hw, _p(gl), _stream())
+        return None, gl, None
+
+
+def _per_ray_cameras(ppc, n, dev):
+    eye = ppc["eye_pos"]
+    if isinstance(eye, (list, tuple)):
+        eye = torch.stack([torch.as_tensor(e) for e in eye])
+    cam_M = ppc["camera"]
+    if isinstance(cam_M, (list, tuple)):
+        cam_M = torch.stack([torch.as_tensor(c) for c in cam_M])
+    return _f32(cam_M, dev).reshape(n, 3, 3), _f32(eye, dev).reshape(n, 3)
+
+
 def get_K_impl(cam_pixels, cam_results, ppc, light_camera, fine_sampling):
-    raise NotImplementedError("get_K (rendering_shadows.py:484-546) belongs to the light-sampler trainer, "
-                              "SURVEY §8f rank 2 ('next'); not built yet")
+    """rendering_shadows.py:484-546: (proj_maps_coarse (n,3), proj_maps_fine (n,3) or None), K = [ul, vl, wl] of every
+    camera ray in the light's image from `depth_coarse` / `depth_fine`.  The reference splits the batch into
+    same-eye_pos runs with a Python loop (one host comparison per ray); here the runs are found on the device."""
+    dc = cam_results["depth_coarse"]
+    dev = dc.device
+    n = dc.numel()
+    cam_M, eye = _per_ray_cameras(ppc, n, dev)
+    inv, _, Leye = _light_static(light_camera, dev)
+    pix = _f32(cam_pixels, dev)
+    coarse = ProjectToLight.apply(dc.reshape(-1), pix, cam_M, eye, inv, Leye, False)
+    fine = None
+    if fine_sampling:
+        fine = ProjectToLight.apply(cam_results["depth_fine"].reshape(-1), pix, cam_M, eye, inv, Leye, False)
+    return coarse, fine

@@ -326,7 +326,8 @@ def shadow_map(wl: Tensor, w_light_b: Tensor, mode: str, delta=1e-2, epsilon=0.0
     if mode == "shadow_method_1":
         diff = torch.max(diff / delta, torch.tensor(epsilon))
     elif mode == "shadow_method_2":
-        diff = (diff - diff.min()) / (diff.max() - diff.min() + SHADOW_EPS) * (new_max - new_min) + new_min
+        # the reference calls normalize_min_max(diff) without forwarding new_min / new_max (:124): they have no effect
+        diff = (diff - diff.min()) / (diff.max() - diff.min() + SHADOW_EPS)
         if sigmoid:
             diff = torch.sigmoid(diff)
     else:
@@ -378,6 +379,33 @@ def efficient_sm(cam_pixels, light_pixels, cam_results, light_results, ppc, ligh
         ld = light_results["depth_fine"] if light_n_importance else light_results["depth_coarse"]
         cam_results[f"{out_prefix}_fine"] = run(cam_results["depth_fine"], ld)
     return cam_results
+
+
+def normalize_min_max(t: Tensor, new_max: float = 1.0, new_min: float = 0.0) -> Tensor:
+    """efficient_shadow_mapping.py:10-11"""
+    return (t - t.min()) / (t.max() - t.min() + SHADOW_EPS) * (new_max - new_min) + new_min
+
+
+def projections(cam_M: Tensor, cam_eye: Tensor, light_M: Tensor, light_eye: Tensor, mesh_range_cam: Tensor) -> Tensor:
+    """get_projections (efficient_shadow_mapping.py:13-17) for one camera: get_normed_w then get_diff_projections."""
+    wc = normed_w(cam_M, mesh_range_cam)
+    R, Q = transformation_to(cam_M, cam_eye, light_M, light_eye)
+    return diff_projections(wc[:, :3], wc[:, 3], R, Q)
+
+
+def get_K(cam_pixels: Tensor, cam_results: Dict[str, Tensor], ppc, light_M: Tensor, light_eye: Tensor,
+          fine_sampling: bool):
+    """rendering_shadows.py:484-546: per same-eye_pos run (each with the camera of its first ray) the projection
+    [ul, vl, wl] of every camera ray into the light's image, for depth_coarse and (optionally) depth_fine."""
+    eye, cams = ppc["eye_pos"], ppc["camera"]
+    segs = camera_segments(eye)
+
+    def run(depth):
+        mrc = torch.cat([cam_pixels, depth.view(-1, 1)], 1)
+        return torch.cat([projections(cams[s], eye[s], light_M, light_eye, mrc[s:e]) for (s, e) in segs], 0).view(-1, 3)
+
+    coarse = run(cam_results["depth_coarse"])
+    return coarse, (run(cam_results["depth_fine"]) if fine_sampling else None)
 
 
 # ---------------------------------------------------------------------------

@@ -218,3 +218,47 @@ def test_oracle_adam_vs_live_torch():
         opt.step()
         q, m, v = O.adam_step(q, gr, m, v, t + 1, 1e-3, eps=1e-8, weight_decay=1e-2)
         assert torch.allclose(q, p.detach(), rtol=0, atol=1e-6)
+
+
+# ---- the light-sampler trainer's shadow-mapping pieces -----------------------------------
+
+def _ls():
+    z = np.load(os.path.join(G, "lightsampler.npz"))
+    return z, (lambda k: torch.from_numpy(z[k]))
+
+
+@pytest.mark.parametrize("tag", ["split", "single"])
+def test_oracle_get_K_vs_reference(tag):
+    z, T = _ls()
+    cd = {k: T(f"getK_{tag}/{k}").clone().requires_grad_() for k in ("depth_coarse", "depth_fine")}
+    ppc = {"eye_pos": T(f"getK_{tag}/eye_pos"), "camera": T(f"getK_{tag}/camera")}
+    Kc, Kf = O.get_K(T(f"getK_{tag}/cam_pixels"), cd, ppc, T("light_camera"), T("light_eye"), True)
+    assert torch.allclose(Kc, T(f"getK_{tag}/K_coarse"), rtol=1e-5, atol=1e-5)
+    assert torch.allclose(Kf, T(f"getK_{tag}/K_fine"), rtol=1e-5, atol=1e-5)
+    probe = T(f"getK_{tag}/probe")
+    ((Kc * probe).sum() + 2 * (Kf * probe).sum()).backward()
+    for k in cd:
+        assert torch.allclose(cd[k].grad, T(f"getK_{tag}/g_{k}"), rtol=1e-4, atol=1e-5), k
+    assert O.get_K(T(f"getK_{tag}/cam_pixels"), cd, ppc, T("light_camera"), T("light_eye"), False)[1] is None
+
+
+def test_oracle_shadow_pieces_vs_reference():
+    z, T = _ls()
+    res = tuple(int(v) for v in z["res"])
+    K = O.projections(T("proj/cam_M"), T("proj/cam_eye"), T("light_camera"), T("light_eye"),
+                      torch.cat([T("proj/pix"), T("proj/depth").view(-1, 1)], 1))
+    assert torch.allclose(K, T("proj/K"), rtol=1e-5, atol=1e-5)
+    R, Q = O.transformation_to(T("proj/cam_M"), T("proj/cam_eye"), T("light_camera"), T("light_eye"))
+    assert torch.allclose(O.diff_projections(T("proj/pix"), T("diffproj/w_cam"), R, Q), T("diffproj/K"), rtol=1e-5, atol=1e-5)
+    wl, wlb = O.projected_depths(res, T("gather/K"), T("gather/w_light"))
+    assert torch.equal(wl, T("gather/wl")) and torch.equal(wlb, T("gather/wlb"))
+    for tag, kw in (("m1", dict(mode="shadow_method_1")), ("m1_eps", dict(mode="shadow_method_1", delta=0.05, epsilon=0.2)),
+                    ("m2", dict(mode="shadow_method_2")), ("m2_sig", dict(mode="shadow_method_2", sigmoid=True)),
+                    ("m2_range", dict(mode="shadow_method_2", new_min=-0.5, new_max=1.5))):
+        a, b = T(f"map_{tag}/wl").clone().requires_grad_(), T(f"map_{tag}/wlb").clone().requires_grad_()
+        sm = O.shadow_map(a, b, **kw)
+        assert torch.allclose(sm, T(f"map_{tag}/out"), rtol=1e-6, atol=1e-7), tag
+        (sm * T(f"map_{tag}/probe")).sum().backward()
+        assert torch.allclose(a.grad, T(f"map_{tag}/g_wl"), rtol=1e-4, atol=1e-5), tag
+        assert torch.allclose(b.grad, T(f"map_{tag}/g_wlb"), rtol=1e-4, atol=1e-5), tag
+    assert torch.allclose(O.normalize_min_max(T("norm/t"), new_max=2.0, new_min=-1.0), T("norm/out"), rtol=1e-6, atol=1e-7)
