@@ -225,21 +225,23 @@ int nrf_normed_w(const float* pixel_depth, const float* value, const float* pass
  * a24 get_K / get_projections / get_diff_projections — models/rendering_shadows.py:484-546,
  * models/efficient_shadow_mapping.py:13-17, :65-83.  K (n,3) = [ul, vl, wl] of every camera ray in the light's image.
  * n_cam = n: cam_M (n,3,3), cam_eye (n,3) per ray, segmented by eye_pos like the reference's loop (seg_ws: n ints);
- * n_cam = 1: one camera for the batch (seg_ws may be NULL).  normalised != 0: cam_depth already is w
- * (get_diff_projections).  g_K == NULL: forward, out = K (n,3); else backward w.r.t. cam_depth, out = g_depth (n). */
+ * n_cam = 1: one camera for the batch (seg_ws may be NULL).  normalised: 0 = cam_depth is a range,
+ * w = depth / (|M pix| + 1e-5) (get_normed_w); 1 = cam_depth already is w (get_diff_projections); 2 = range without
+ * the epsilon (models/shadow_mapping_utils.py:39-66, whole-image variant).  g_K == NULL: forward, out = K (n,3); else backward w.r.t. cam_depth, out = g_depth (n). */
 int nrf_project_to_light(const float* cam_pixels, const float* cam_depth, const float* cam_M, const float* cam_eye,
                          int64_t n_cam, const float* light_Minv, const float* light_eye, int64_t n, int normalised,
                          const float* g_K, float* out, int* seg_ws, nrf_stream_t stream);
 /* a25 generate_shadow_map / normalize_min_max — models/efficient_shadow_mapping.py:10-11, :103-130 on explicit
- * vectors: diff = wl - w_light_bounded (w_light_bounded NULL: diff = wl).  stack_clip != 0: out (n,3) = stack and
- * clip(0,1) (generate_shadow_map); 0: out (n) (mode 2 without sigmoid = normalize_min_max).
+ * vectors: diff = wl - w_light_bounded (w_light_bounded NULL: diff = wl).  flags bit 0 (stack_clip): out (n,3) = stack and
+ * clip(0,1) (generate_shadow_map), else out (n) (mode 2 without sigmoid = normalize_min_max); flags bit 1: min-max
+ * normalisation without the 1e-5 in the denominator (models/shadow_mapping_utils.py:8-9, :149-174).
  * Backward: g_out -> g_diff (n) (= d/dwl; d/dw_light_bounded is its negative).  workspace: 32 bytes. */
 size_t nrf_shadow_map_workspace_bytes(void);
 int nrf_shadow_map_fwd(const float* wl, const float* w_light_bounded, int64_t n, int mode, float delta, float epsilon,
-                       float new_min, float new_max, int sigmoid, int stack_clip, float* out, void* workspace,
+                       float new_min, float new_max, int sigmoid, int flags, float* out, void* workspace,
                        nrf_stream_t stream);
 int nrf_shadow_map_bwd(const float* wl, const float* w_light_bounded, int64_t n, int mode, float delta, float epsilon,
-                       float new_min, float new_max, int sigmoid, int stack_clip, const float* g_out, float* g_diff,
+                       float new_min, float new_max, int sigmoid, int flags, const float* g_out, float* g_diff,
                        void* workspace, nrf_stream_t stream);
 /* a26 get_projected_depths — models/efficient_shadow_mapping.py:85-100: w_light_bounded[i] =
  * w_light.view(w,h)[clamp(vl), clamp(ul)] (truncated), gidx[i] = the flat index read.  nrf_light_scatter is its
@@ -248,6 +250,11 @@ int nrf_light_gather(const float* K, const float* w_light, int64_t n, int res_w,
                      int* gidx, nrf_stream_t stream);
 int nrf_light_scatter(const float* g_wlb, const int* gidx, int64_t n, int64_t n_light, float* g_wlight,
                       nrf_stream_t stream);
+/* a27 differentiable_w_mapping — models/shadow_mapping_utils.py:39-66 (whole-image shadow mapping of
+ * train_shadow_mapping.py): out (n) = value / (|M pixels_i| + eps), pixels (n,3) = [i+.5, j+.5, 1]; eps = 0 there.
+ * Linear in value: the backward is the same call with value = grad_out. */
+int nrf_w_mapping(const float* pixels, const float* value, const float* M, int64_t n, float eps, float* out,
+                  nrf_stream_t stream);
 
 /* Diagnostics (not on the product path): lane-parallel cp.async.bulk streaming benchmark used to choose
  * the stash layout and the weight-ring geometry (tools/stream_bench.py).  Moves

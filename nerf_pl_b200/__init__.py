@@ -12,7 +12,8 @@ def install_as_models():
     import importlib
     pkg = importlib.import_module("nerf_pl_b200.models")
     sys.modules["models"] = pkg
-    for sub in ("nerf", "rendering", "rendering_shadows", "rendering_rgb_sm", "efficient_shadow_mapping", "camera"):
+    for sub in ("nerf", "rendering", "rendering_shadows", "rendering_rgb_sm", "efficient_shadow_mapping", "shadow_mapping_utils",
+                "camera"):
         sys.modules[f"models.{sub}"] = importlib.import_module(f"nerf_pl_b200.models.{sub}")
     ts = importlib.import_module("nerf_pl_b200.torchsearchsorted")
     sys.modules.setdefault("torchsearchsorted", ts)

@@ -69,6 +69,7 @@ SIGNATURES = {
     "nrf_shadow_map_bwd": (I, [P, P, L, I, F, F, F, F, I, I, P, P, P, P]),
     "nrf_light_gather": (I, [P, P, L, I, I, P, P, P]),
     "nrf_light_scatter": (I, [P, P, L, L, P, P]),
+    "nrf_w_mapping": (I, [P, P, P, L, F, P, P]),
     "nrf_dbg_set_counters": (None, [P]),
     "nrf_dbg_mma_rate": (I, [I, I, P, P]),
     "nrf_dbg_store_rate": (I, [P, ctypes.c_uint64, c_uint32, I, I, I, P, P]),

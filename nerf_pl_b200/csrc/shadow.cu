@@ -178,11 +178,12 @@ __global__ void project_kernel(const float* __restrict__ cam_pixels, const float
 struct ShadowCfg {
   int mode, sigmoid;
   float delta, epsilon, new_min, new_max, out_bias;
+  float norm_eps = kShadowEps;  // 0 for models/shadow_mapping_utils.py:8-9 (whole-image variant, no epsilon)
 };
 
 __device__ __forceinline__ float shadow_value(float d, float mn, float mx, const ShadowCfg& cfg) {
   if (cfg.mode == 1) return fmaxf(d / cfg.delta, cfg.epsilon);  // :119-121
-  float y = (d - mn) / (mx - mn + kShadowEps) * (cfg.new_max - cfg.new_min) + cfg.new_min;  // :10-11
+  float y = (d - mn) / (mx - mn + cfg.norm_eps) * (cfg.new_max - cfg.new_min) + cfg.new_min;  // :10-11
   if (cfg.sigmoid) y = 1.0f / (1.0f + expf(-y));
   return y;
 }
@@ -414,7 +415,7 @@ __device__ __forceinline__ ProjCam proj_setup(const float* __restrict__ M, const
                                               float a, float b, float c, int normalised) {
   ProjCam pc;
   const float cx = mat_row_dot(M, 0, a, b, c), cy = mat_row_dot(M, 1, a, b, c), cz = mat_row_dot(M, 2, a, b, c);
-  pc.nrm = normalised ? 1.0f : sqrtf(cx * cx + cy * cy + cz * cz) + kShadowEps;
+  pc.nrm = normalised == 1 ? 1.0f : sqrtf(cx * cx + cy * cy + cz * cz) + (normalised == 2 ? 0.0f : kShadowEps);
   const float ex = eye[0] - light_eye[0], ey = eye[1] - light_eye[1], ez = eye[2] - light_eye[2];
 #pragma unroll
   for (int r = 0; r < 3; ++r) {
@@ -537,7 +538,7 @@ __global__ void map_bwd_apply_kernel(const float* __restrict__ g_out, const floa
   float mn = 0.f, mx = 0.f, D = 1.f, g_mn = 0.f, g_mx = 0.f;
   if (cfg.mode == 2) {
     mn = key_float(w.keys[0]); mx = key_float(w.keys[1]);
-    D = mx - mn + kShadowEps;
+    D = mx - mn + cfg.norm_eps;
     g_mn = (-w.sums[0] / D + w.sums[1] / (D * D)) / (float)max(w.cnt[0], 1);   // through tensor.min()
     g_mx = (-w.sums[1] / (D * D)) / (float)max(w.cnt[1], 1);                    // through tensor.max()
   }
@@ -615,14 +616,16 @@ static int map_check(const char* who, const float* wl, int64_t n, int mode, void
 }
 
 extern "C" int nrf_shadow_map_fwd(const float* wl, const float* w_light_bounded, int64_t n, int mode, float delta,
-                                  float epsilon, float new_min, float new_max, int sigmoid, int stack_clip, float* out,
+                                  float epsilon, float new_min, float new_max, int sigmoid, int flags, float* out,
                                   void* workspace, nrf_stream_t stream) {
   int rc = map_check("nrf_shadow_map_fwd", wl, n, mode, workspace);
   if (rc || n == 0) return rc;
   NRF_REQUIRE(out != nullptr, "nrf_shadow_map_fwd: null output");
   cudaStream_t st = as_stream(stream);
   const MapWs w = map_carve(workspace);
-  const ShadowCfg cfg{mode, sigmoid, delta, epsilon, new_min, new_max, 0.f};
+  ShadowCfg cfg{mode, sigmoid, delta, epsilon, new_min, new_max, 0.f};
+  if (flags & 2) cfg.norm_eps = 0.f;
+  const int stack_clip = flags & 1;
   if (mode == 2) {
     map_init_kernel<<<1, 1, 0, st>>>(w);
     NRF_LAUNCH_CHECK();
@@ -635,14 +638,16 @@ extern "C" int nrf_shadow_map_fwd(const float* wl, const float* w_light_bounded,
 }
 
 extern "C" int nrf_shadow_map_bwd(const float* wl, const float* w_light_bounded, int64_t n, int mode, float delta,
-                                  float epsilon, float new_min, float new_max, int sigmoid, int stack_clip,
+                                  float epsilon, float new_min, float new_max, int sigmoid, int flags,
                                   const float* g_out, float* g_diff, void* workspace, nrf_stream_t stream) {
   int rc = map_check("nrf_shadow_map_bwd", wl, n, mode, workspace);
   if (rc || n == 0) return rc;
   NRF_REQUIRE(g_out && g_diff, "nrf_shadow_map_bwd: null pointer");
   cudaStream_t st = as_stream(stream);
   const MapWs w = map_carve(workspace);
-  const ShadowCfg cfg{mode, sigmoid, delta, epsilon, new_min, new_max, 0.f};
+  ShadowCfg cfg{mode, sigmoid, delta, epsilon, new_min, new_max, 0.f};
+  if (flags & 2) cfg.norm_eps = 0.f;
+  const int stack_clip = flags & 1;
   if (mode == 2) {
     map_init_kernel<<<1, 1, 0, st>>>(w);
     NRF_LAUNCH_CHECK();
@@ -677,6 +682,30 @@ extern "C" int nrf_light_scatter(const float* g_wlb, const int* gidx, int64_t n,
   if (n == 0) return NRF_OK;
   NRF_REQUIRE(g_wlb && gidx, "nrf_light_scatter: null pointer");
   light_scatter_kernel<<<sgrid(n), 256, 0, as_stream(stream)>>>(g_wlb, gidx, n, g_wlight);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+
+// a27 whole-image range -> w (models/shadow_mapping_utils.py:39-66): w = range / |M [i+.5, j+.5, 1]^T| for explicit pixel
+// rows, no epsilon unless asked for.  Linear in `value`, so the backward is the same launch with value = grad_out.
+namespace nrf {
+__global__ void w_mapping_kernel(const float* __restrict__ pixels, const float* __restrict__ value,
+                                 const float* __restrict__ M, int64_t n, float eps, float* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float a = pixels[i * 3], b = pixels[i * 3 + 1], c = pixels[i * 3 + 2];
+    const float x = mat_row_dot(M, 0, a, b, c), y = mat_row_dot(M, 1, a, b, c), zc = mat_row_dot(M, 2, a, b, c);
+    out[i] = value[i] / (sqrtf(x * x + y * y + zc * zc) + eps);
+  }
+}
+}  // namespace nrf
+
+extern "C" int nrf_w_mapping(const float* pixels, const float* value, const float* M, int64_t n, float eps, float* out,
+                             nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0, "nrf_w_mapping: bad size");
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(pixels && value && M && out, "nrf_w_mapping: null pointer");
+  nrf::w_mapping_kernel<<<nrf::sgrid(n), 256, 0, nrf::as_stream(stream)>>>(pixels, value, M, n, eps, out);
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

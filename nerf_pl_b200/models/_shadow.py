@@ -106,7 +106,7 @@ class ProjectToLight(torch.autograd.Function):
         seg = torch.empty(n, dtype=torch.int32, device=depth.device) if n_cam != 1 else None
         out = torch.empty(n, 3, device=depth.device)
         ctx.args = (_p(cam_pixels), _p(depth), _p(cam_M), _p(cam_eye), n_cam, _p(light_Minv), _p(light_eye), n,
-                    int(bool(normalised)))
+                    int(normalised))      # 0 range with the 1e-5 guard, 1 already w, 2 range without the guard
         ctx.keep = (cam_pixels, cam_M, cam_eye, light_Minv, light_eye, seg)
         ctx.save_for_backward(depth)
         _lib.call("nrf_project_to_light", *ctx.args, None, _p(out), _p(seg), _stream())
@@ -126,7 +126,7 @@ class ShadowMap(torch.autograd.Function):
     stack_clip: (n,3) stacked and clipped output; otherwise (n,)."""
 
     @staticmethod
-    def forward(ctx, wl, wlb, mode, delta, epsilon, new_min, new_max, sigmoid, stack_clip):
+    def forward(ctx, wl, wlb, mode, delta, epsilon, new_min, new_max, sigmoid, stack_clip, no_eps=False):
         if mode not in _MODES:
             raise ValueError("{} not found".format(mode))
         wl = _dev(wl, "wl").reshape(-1)
@@ -140,7 +140,7 @@ class ShadowMap(torch.autograd.Function):
         if stack_clip:       # generate_shadow_map ignores new_min / new_max (efficient_shadow_mapping.py:124)
             new_min, new_max = 0.0, 1.0
         ctx.args = (_p(wl), _p(wlb), n, _MODES[mode], float(delta), float(epsilon), float(new_min), float(new_max),
-                    int(bool(sigmoid)), int(bool(stack_clip)))
+                    int(bool(sigmoid)), int(bool(stack_clip)) | (2 if no_eps else 0))
         ctx.keep = (wl, wlb)
         ctx.has_b = wlb is not None
         _lib.call("nrf_shadow_map_fwd", *ctx.args, _p(out), _p(ws), _stream())
@@ -153,7 +153,7 @@ class ShadowMap(torch.autograd.Function):
         gd = torch.empty_like(wl)
         ws = torch.empty(32, dtype=torch.uint8, device=wl.device)
         _lib.call("nrf_shadow_map_bwd", *ctx.args, _p(g), _p(gd), _p(ws), _stream())
-        return (gd, -gd if ctx.has_b and ctx.needs_input_grad[1] else None) + (None,) * 7
+        return (gd, -gd if ctx.has_b and ctx.needs_input_grad[1] else None) + (None,) * 8
 
 
 class LightGather(torch.autograd.Function):
@@ -208,3 +208,43 @@ def get_K_impl(cam_pixels, cam_results, ppc, light_camera, fine_sampling):
     if fine_sampling:
         fine = ProjectToLight.apply(cam_results["depth_fine"].reshape(-1), pix, cam_M, eye, inv, Leye, False)
     return coarse, fine
+
+
+def shadow_mapping_impl(cam_results, light_results, rays, ppc, light_ppc, image_shape, batch_size, fine_sampling):
+    """Whole-image shadow mapping of train_shadow_mapping.py (rendering_shadows.py:283-353, twin
+    rendering_rgb_sm.py:280-350): depth_* of `batch_size` full camera images and of the light image -> `rgb_coarse`
+    (and `rgb_fine`) = (batch_size*H*W, 3) shadow images, 'shadow_method_2'.
+
+    The reference's body hands (H,W) depth images to efficient_shadow_mapping.run_shadow_mapping, which takes (n,4) ray
+    lists, and raises (`shape '[W, H]' is invalid`, probed in the build container); what runs here is the whole-image
+    stack the function was written against, models/shadow_mapping_utils.run_shadow_mapping (:11-36), per image.  Like
+    the reference (:351) `rgb_fine` is assigned the COARSE shadow images."""
+    from . import shadow_mapping_utils as smu
+    from .camera import Camera
+    N_rays = rays.shape[0]
+    W, H = image_shape
+
+    def images(key):
+        cam, light = cam_results[key], light_results[key]
+        assert N_rays == cam.shape[0]
+        assert N_rays == light.shape[0]
+        return cam.view(batch_size, H, W), light.view(batch_size, H, W)
+
+    def inference(cam_depths, light_depths):
+        light_cam = Camera.from_camera_eyepos(eye_pos=torch.as_tensor(light_ppc['eye_pos']).squeeze(0),
+                                              camera=torch.as_tensor(light_ppc['camera']).squeeze(0))
+        maps = []
+        for i in range(batch_size):
+            cam = Camera.from_camera_eyepos(eye_pos=torch.as_tensor(ppc[i]['eye_pos']).squeeze(0),
+                                            camera=torch.as_tensor(ppc[i]['camera']).squeeze(0))
+            maps.append(smu.run_shadow_mapping(image_shape, cam, light_cam, cam_depths[i], light_depths[i],
+                                               device=cam_depths.device, mode='shadow_method_2', delta=1e-2, epsilon=0.0,
+                                               new_min=0.0, new_max=1.0, sigmoid=False, use_numpy_meshgrid=True))
+        return torch.cat(maps, 0).view(-1, 3)
+
+    shadow_maps_coarse = inference(*images('depth_coarse'))
+    cam_results['rgb_coarse'] = shadow_maps_coarse
+    if fine_sampling:
+        images('depth_fine')                  # shape checks only: the reference computes the fine maps and drops them
+        cam_results['rgb_fine'] = shadow_maps_coarse
+    return cam_results

@@ -1,9 +1,9 @@
 """Drop-in for models/rendering_rgb_sm.py: rgb renderer + disp_map_* (reference :87-278) and the
 efficient_sm twin that writes sm_coarse / sm_fine (reference :356-480)."""
 from ._render import render_rays_impl, sample_pdf  # noqa: F401
-from ._shadow import efficient_sm_impl, get_K_impl
+from ._shadow import efficient_sm_impl, get_K_impl, shadow_mapping_impl
 
-__all__ = ['render_rays', 'efficient_sm']
+__all__ = ['render_rays', 'shadow_mapping', 'efficient_sm']
 
 
 def render_rays(models, embeddings, rays, N_samples=64, use_disp=False, perturb=0, noise_std=1, N_importance=0,
@@ -20,3 +20,7 @@ def efficient_sm(cam_pixels, light_pixels, cam_results, light_results, ppc, ligh
 
 def get_K(cam_pixels, cam_results, ppc, light_camera, fine_sampling):
     return get_K_impl(cam_pixels, cam_results, ppc, light_camera, fine_sampling)
+
+
+def shadow_mapping(cam_results, light_results, rays, ppc, light_ppc, image_shape, batch_size, fine_sampling):
+    return shadow_mapping_impl(cam_results, light_results, rays, ppc, light_ppc, image_shape, batch_size, fine_sampling)

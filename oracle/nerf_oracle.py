@@ -409,6 +409,70 @@ def get_K(cam_pixels: Tensor, cam_results: Dict[str, Tensor], ppc, light_M: Tens
 
 
 # ---------------------------------------------------------------------------
+# models/shadow_mapping_utils.py: whole-image shadow mapping (train_shadow_mapping.py)
+# ---------------------------------------------------------------------------
+
+def image_pixels(res: Tuple[int, int]) -> Tensor:
+    """(w,h,3) grid [i+.5, j+.5, 1] with i the column index (shadow_mapping_utils.py:46-58)."""
+    w, h = res
+    i = (torch.arange(h, dtype=torch.float32) + 0.5).view(1, h).expand(w, h)
+    j = (torch.arange(w, dtype=torch.float32) + 0.5).view(w, 1).expand(w, h)
+    return torch.stack([i, j, torch.ones(w, h)], -1)
+
+
+def image_w_mapping(res, M: Tensor, range_img: Tensor) -> Tensor:
+    """range (w,h) -> w = range / |M pix| -- no epsilon (shadow_mapping_utils.py:39-66)."""
+    coords = (image_pixels(res)[..., None, :] * M).sum(-1)
+    return range_img / torch.linalg.norm(coords, dim=2)
+
+
+def image_projections(res, w_cam: Tensor, cam_M, cam_eye, light_M, light_eye) -> Tensor:
+    """K (w,h,3) (shadow_mapping_utils.py:68-104)."""
+    R, Q = transformation_to(cam_M, cam_eye, light_M, light_eye)
+    proj = (image_pixels(res)[..., None, :] * R).sum(-1)
+    uvw = w_cam[..., None] * proj + Q
+    wl = uvw[..., 2]
+    return torch.stack([uvw[..., 0] / wl, uvw[..., 1] / wl, wl], 2)
+
+
+def image_depths(res, K: Tensor, w_light: Tensor):
+    """(wl, w_light_bounded, ul_, vl_) (shadow_mapping_utils.py:106-147); K[j,i] is the identity on a square grid."""
+    w, h = res
+    ul_, vl_, wl = K.unbind(2)
+    ul = ul_.clamp(min=0.0).clamp(max=w - 1.0).long()
+    vl = vl_.clamp(min=0.0).clamp(max=h - 1.0).long()
+    return wl, w_light[vl, ul], ul_, vl_
+
+
+def image_normalize_min_max(t: Tensor, new_max: float = 1.0, new_min: float = 0.0) -> Tensor:
+    """shadow_mapping_utils.py:8-9 (no epsilon in the denominator)."""
+    return (t - t.min()) / (t.max() - t.min()) * (new_max - new_min) + new_min
+
+
+def image_shadow_map(wl: Tensor, w_light_b: Tensor, mode: str, delta=1e-2, epsilon=0.0, sigmoid=False) -> Tensor:
+    """(w,h,3) (shadow_mapping_utils.py:149-174)."""
+    diff = wl - w_light_b
+    if mode == "shadow_method_1":
+        diff = torch.max(diff / delta, torch.tensor(epsilon))
+    elif mode == "shadow_method_2":
+        diff = image_normalize_min_max(diff)
+        if sigmoid:
+            diff = torch.sigmoid(diff)
+    else:
+        raise ValueError("{} not found".format(mode))
+    return torch.stack([diff, diff, diff], 2).clip(0.0, 1.0)
+
+
+def image_run_shadow_mapping(res, cam_M, cam_eye, light_M, light_eye, range_cam, range_light, mode, **kw) -> Tensor:
+    """shadow_mapping_utils.py:11-36"""
+    w_cam = image_w_mapping(res, cam_M, range_cam)
+    w_light = image_w_mapping(res, light_M, range_light)
+    K = image_projections(res, w_cam, cam_M, cam_eye, light_M, light_eye)
+    wl, wlb, _, _ = image_depths(res, K, w_light)
+    return image_shadow_map(wl, wlb, mode, **kw)
+
+
+# ---------------------------------------------------------------------------
 # Synthetic inputs (SURVEY §8d).  Ray generation restates datasets/ray_utils.py:5-50.
 # ---------------------------------------------------------------------------
 

@@ -262,3 +262,43 @@ def test_oracle_shadow_pieces_vs_reference():
         assert torch.allclose(a.grad, T(f"map_{tag}/g_wl"), rtol=1e-4, atol=1e-5), tag
         assert torch.allclose(b.grad, T(f"map_{tag}/g_wlb"), rtol=1e-4, atol=1e-5), tag
     assert torch.allclose(O.normalize_min_max(T("norm/t"), new_max=2.0, new_min=-1.0), T("norm/out"), rtol=1e-6, atol=1e-7)
+
+
+# ---- whole-image shadow mapping (models/shadow_mapping_utils.py), tests/make_golden_shadow_image.py ----------------------
+def _si():
+    z = np.load(os.path.join(G, "shadow_image.npz"))
+    return z, (lambda k: torch.from_numpy(z[k]))
+
+
+def test_oracle_shadow_image_pieces_vs_reference():
+    z, T = _si()
+    res = tuple(int(v) for v in z["res"])
+    assert int(z["wrapper_raises"]) == 1        # rendering_shadows.shadow_mapping() raises in the reference
+    assert torch.allclose(O.image_w_mapping(res, T("cam_M"), T("wmap/range")), T("wmap/w"), rtol=1e-6, atol=0)
+    K = O.image_projections(res, T("proj/w_cam"), T("cam_M"), T("cam_eye"), T("light_M"), T("light_eye"))
+    assert torch.allclose(K, T("proj/K"), rtol=1e-5, atol=1e-5)
+    wl, wlb, ul_, vl_ = O.image_depths(res, T("depths/K"), T("depths/w_light"))
+    assert torch.equal(wl, T("depths/wl")) and torch.equal(wlb, T("depths/wlb"))
+    for tag, kw in (("m1", dict(mode="shadow_method_1")), ("m1_eps", dict(mode="shadow_method_1", delta=0.05, epsilon=0.2)),
+                    ("m2", dict(mode="shadow_method_2")), ("m2_sig", dict(mode="shadow_method_2", sigmoid=True)),
+                    ("m2_range", dict(mode="shadow_method_2"))):
+        a, b = T(f"map_{tag}/wl").clone().requires_grad_(), T(f"map_{tag}/wlb").clone().requires_grad_()
+        sm = O.image_shadow_map(a, b, **kw)
+        assert torch.allclose(sm, T(f"map_{tag}/out"), rtol=1e-6, atol=1e-7), tag
+        (sm * T(f"map_{tag}/probe")).sum().backward()
+        assert torch.allclose(a.grad, T(f"map_{tag}/g_wl"), rtol=1e-4, atol=1e-5), tag
+        assert torch.allclose(b.grad, T(f"map_{tag}/g_wlb"), rtol=1e-4, atol=1e-5), tag
+    assert torch.allclose(O.image_normalize_min_max(T("norm/t"), new_max=2.0, new_min=-1.0), T("norm/out"), rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("tag,mode", [("run_m1", "shadow_method_1"), ("run_m2", "shadow_method_2")])
+def test_oracle_shadow_image_run_vs_reference(tag, mode):
+    z, T = _si()
+    res = tuple(int(v) for v in z["res"])
+    rc, rl = T(f"{tag}/range_cam").clone().requires_grad_(), T(f"{tag}/range_light").clone().requires_grad_()
+    sm = O.image_run_shadow_mapping(res, T("cam_M"), T("cam_eye"), T("light_M"), T("light_eye"), rc, rl, mode)
+    assert torch.allclose(sm, T(f"{tag}/out"), rtol=1e-5, atol=1e-6)
+    (sm * T(f"{tag}/probe")).sum().backward()
+    for g, k in ((rc.grad, "g_range_cam"), (rl.grad, "g_range_light")):
+        ref = T(f"{tag}/{k}")
+        assert torch.allclose(g, ref, rtol=1e-4, atol=1e-5 * float(ref.abs().max())), k
