@@ -86,6 +86,18 @@ int nrf_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
 size_t nrf_adam_state_bytes(void);
 int nrf_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double beta1,
                       double beta2, double eps, double weight_decay, void* state, nrf_stream_t stream);
+/* a28 the reference's other optimizers over the same flat buffers (utils/__init__.py:14-27).
+ * nrf_sgd_step: torch.optim.SGD(lr, momentum, weight_decay) — L2 term added to the gradient, momentum buffer seeded
+ * with the first gradient (first_step != 0), dampening 0, no nesterov; momentum_buf may be NULL when momentum == 0.
+ * nrf_radam_step: ranger == 0: RAdam (utils/optimizers.py:6-95; rectified when N_sma >= 5, else the SGD-like step when
+ * degenerated_to_sgd, else moments only); ranger != 0: Ranger (utils/optimizers.py:266-404; threshold N_sma >
+ * n_sma_threshold, lookahead slow += alpha (p - slow), p = slow every k steps; `slow` holds the initial parameters before
+ * the first step).  `step` counts from 1.  Weight decay multiplies the parameter (p += -wd*lr*p) ahead of the update. */
+int nrf_sgd_step(float* param, const float* grad, float* momentum_buf, int64_t n, double lr, double momentum,
+                 double weight_decay, int first_step, nrf_stream_t stream);
+int nrf_radam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* slow, int64_t n, double lr,
+                   double beta1, double beta2, double eps, double weight_decay, int64_t step, int ranger,
+                   double n_sma_threshold, int degenerated_to_sgd, double alpha, int k, nrf_stream_t stream);
 
 /* a4  stratified depth sampling — models/rendering.py:216-232
  * rays (N,8) = [o(3) d(3) near far]; t_steps (n_samples) = linspace(0,1,n_samples);

@@ -42,6 +42,8 @@ SIGNATURES = {
     "nrf_adam_step": (I, [P, P, P, P, L, D, D, D, D, D, L, P]),
     "nrf_adam_state_bytes": (Z, []),
     "nrf_adam_step_dev": (I, [P, P, P, P, L, D, D, D, D, P, P]),
+    "nrf_sgd_step": (I, [P, P, P, L, D, D, D, I, P]),
+    "nrf_radam_step": (I, [P, P, P, P, P, L, D, D, D, D, D, L, I, D, I, D, I, P]),
     "nrf_sample_coarse": (I, [P, P, L, I, I, F, P, P, P]),
     "nrf_embed_fwd": (I, [P, L, I, P, I, P, P]),
     "nrf_embed_bwd": (I, [P, P, L, I, P, I, P, P]),

@@ -306,3 +306,107 @@ extern "C" int nrf_adam_step_dev(float* param, const float* grad, float* exp_avg
   k.w2 = (float)(1.0 - beta2);
   return adam_launch(param, grad, exp_avg, exp_avg_sq, n, k, st, as_stream(stream));
 }
+
+// ---- a28 the reference's other optimizers over the same flat buffers (utils/__init__.py:14-27) -------
+// sgd    torch.optim.SGD(lr, momentum, weight_decay): L2 term added to the gradient, momentum buffer seeded with the first
+//        gradient, dampening 0, no nesterov.
+// radam  utils/optimizers.py:6-95: raw-gradient moments, rectified step (N_sma >= 5) or the SGD-like fallback, weight
+//        decay applied to the parameter (p += -wd*lr*p) ahead of the update.
+// ranger utils/optimizers.py:266-404: RAdam (threshold N_sma > N_sma_threshhold, decay always applied) + lookahead every
+//        k steps (slow += alpha (p - slow); p = slow), slow buffer seeded with the initial parameters by the caller.
+// The step-dependent scalars (N_sma, step_size) are computed on the host in double like the reference's Python floats.
+namespace nrf {
+struct RAdamK {
+  float beta1, beta2, w1, w2, eps, decay, step, alpha;   // decay = -wd*lr, step = -step_size*lr
+  int rectified, update, lookahead;
+};
+
+__device__ __forceinline__ void radam_one(float& p, float g, float& m, float& v, float* slow, const RAdamK& k) {
+  v = v * k.beta2 + k.w2 * g * g;                    // exp_avg_sq.mul_(beta2).addcmul_(1 - beta2, grad, grad)
+  m = m * k.beta1 + k.w1 * g;                        // exp_avg.mul_(beta1).add_(1 - beta1, grad)
+  if (k.update) {
+    if (k.decay != 0.f) p = p + k.decay * p;
+    if (k.rectified) p = p + k.step * (m / (sqrtf(v) + k.eps));
+    else p = p + k.step * m;
+  }
+  if (k.lookahead) {
+    const float s = *slow + k.alpha * (p - *slow);
+    *slow = s;
+    p = s;
+  }
+}
+
+__global__ void __launch_bounds__(256) radam_step_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                         float* __restrict__ m, float* __restrict__ v,
+                                                         float* __restrict__ slow, int64_t n, RAdamK k) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    radam_one(p[i], g[i], m[i], v[i], slow ? slow + i : nullptr, k);
+}
+
+__global__ void __launch_bounds__(256) sgd_step_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                       float* __restrict__ buf, int64_t n, float lr, float momentum,
+                                                       float weight_decay, int first) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float d = g[i];
+    if (weight_decay != 0.f) d = fmaf(weight_decay, p[i], d);          // grad.add(param, alpha=weight_decay)
+    if (buf) {
+      d = first ? d : buf[i] * momentum + d;                           // buf.mul_(momentum).add_(grad)
+      buf[i] = d;
+    }
+    p[i] = p[i] - lr * d;                                              // param.add_(grad, alpha=-lr)
+  }
+}
+
+static inline int eltwise_grid(int64_t n) {
+  const int64_t want = (n + 255) / 256;
+  return (int)(want < 1 ? 1 : (want < (int64_t)kNumSMs * 8 ? want : (int64_t)kNumSMs * 8));
+}
+}  // namespace nrf
+
+extern "C" int nrf_sgd_step(float* param, const float* grad, float* momentum_buf, int64_t n, double lr, double momentum,
+                            double weight_decay, int first_step, nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0, "nrf_sgd_step: bad size");
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(param && grad, "nrf_sgd_step: null pointer");
+  NRF_REQUIRE(momentum == 0.0 || momentum_buf, "nrf_sgd_step: momentum %g needs a buffer", momentum);
+  nrf::sgd_step_kernel<<<nrf::eltwise_grid(n), 256, 0, as_stream(stream)>>>(
+      param, grad, momentum != 0.0 ? momentum_buf : nullptr, n, (float)lr, (float)momentum, (float)weight_decay, first_step);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" int nrf_radam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* slow, int64_t n,
+                              double lr, double beta1, double beta2, double eps, double weight_decay, int64_t step,
+                              int ranger, double n_sma_threshold, int degenerated_to_sgd, double alpha, int k,
+                              nrf_stream_t stream) {
+  NRF_REQUIRE(n >= 0 && step >= 1, "nrf_radam_step: bad size or step");
+  NRF_REQUIRE(!ranger || k >= 1, "nrf_radam_step: lookahead period must be >= 1");
+  if (n == 0) return NRF_OK;
+  NRF_REQUIRE(param && grad && exp_avg && exp_avg_sq && (!ranger || slow), "nrf_radam_step: null pointer");
+  // utils/optimizers.py:66-80 (RAdam), :363-373 (Ranger), in double like the Python floats
+  const double beta2_t = std::pow(beta2, (double)step);
+  const double n_sma_max = 2.0 / (1.0 - beta2) - 1.0;
+  const double n_sma = n_sma_max - 2.0 * (double)step * beta2_t / (1.0 - beta2_t);
+  const double bc1 = 1.0 - std::pow(beta1, (double)step);
+  const bool rect = ranger ? n_sma > n_sma_threshold : n_sma >= 5.0;
+  double step_size;
+  if (rect)
+    step_size = std::sqrt((1.0 - beta2_t) * (n_sma - 4.0) / (n_sma_max - 4.0) * (n_sma - 2.0) / n_sma * n_sma_max /
+                          (n_sma_max - 2.0)) / bc1;
+  else
+    step_size = (ranger || degenerated_to_sgd) ? 1.0 / bc1 : -1.0;
+  nrf::RAdamK kk;
+  kk.beta1 = (float)beta1; kk.beta2 = (float)beta2;
+  kk.w1 = (float)(1.0 - beta1); kk.w2 = (float)(1.0 - beta2);
+  kk.eps = (float)eps;
+  kk.decay = weight_decay != 0.0 ? (float)(-weight_decay * lr) : 0.f;
+  kk.step = (float)(-step_size * lr);
+  kk.alpha = (float)alpha;
+  kk.rectified = rect;
+  kk.update = rect || step_size > 0.0;
+  kk.lookahead = ranger && (step % k == 0);
+  nrf::radam_step_kernel<<<nrf::eltwise_grid(n), 256, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq,
+                                                                               ranger ? slow : nullptr, n, kk);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}

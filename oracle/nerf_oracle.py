@@ -588,3 +588,68 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
     step_size = lr / (1 - b1 ** step)
     denom = v.sqrt() / math.sqrt(1 - b2 ** step) + eps
     return param - step_size * m / denom, m, v
+
+
+def sgd_step(param: Tensor, grad: Tensor, buf: Optional[Tensor], lr: float, momentum: float = 0.0,
+             weight_decay: float = 0.0):
+    """One step of `SGD(parameters, lr, momentum, weight_decay)` (utils/__init__.py:14-16; algorithm in the reference's
+    dependency torch): L2 term added to the gradient, momentum buffer seeded with the first gradient (buf None),
+    dampening 0, no nesterov.  Returns (param, buf)."""
+    g = grad + weight_decay * param if weight_decay != 0 else grad
+    if momentum != 0:
+        buf = g.clone() if buf is None else momentum * buf + g
+        g = buf
+    return param - lr * g, buf
+
+
+def _radam_scalars(step: int, beta1: float, beta2: float):
+    """(N_sma, N_sma_max, rectified step size, sgd-like step size) in Python floats (utils/optimizers.py:66-78)."""
+    beta2_t = beta2 ** step
+    n_sma_max = 2 / (1 - beta2) - 1
+    n_sma = n_sma_max - 2 * step * beta2_t / (1 - beta2_t)
+    rect = None
+    if n_sma > 4:
+        rect = math.sqrt((1 - beta2_t) * (n_sma - 4) / (n_sma_max - 4) * (n_sma - 2) / n_sma * n_sma_max /
+                         (n_sma_max - 2)) / (1 - beta1 ** step)
+    return n_sma, rect, 1.0 / (1 - beta1 ** step)
+
+
+def radam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, step: int, lr: float,
+               betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0, degenerated_to_sgd: bool = True):
+    """utils/optimizers.py:29-95.  Returns (param, exp_avg, exp_avg_sq)."""
+    b1, b2 = betas
+    v = exp_avg_sq * b2 + (1 - b2) * grad * grad
+    m = exp_avg * b1 + (1 - b1) * grad
+    n_sma, rect, plain = _radam_scalars(step, b1, b2)
+    p = param
+    if n_sma >= 5:
+        if weight_decay != 0:
+            p = p + (-weight_decay * lr) * p
+        p = p + (-rect * lr) * (m / (v.sqrt() + eps))
+    elif degenerated_to_sgd:
+        if weight_decay != 0:
+            p = p + (-weight_decay * lr) * p
+        p = p + (-plain * lr) * m
+    return p, m, v
+
+
+def ranger_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, slow: Tensor, step: int, lr: float,
+                alpha: float = 0.5, k: int = 6, n_sma_threshold: float = 5, betas=(0.95, 0.999), eps: float = 1e-5,
+                weight_decay: float = 0.0):
+    """utils/optimizers.py:322-404; `slow` starts as a copy of the initial parameters (:347-348).
+    Returns (param, exp_avg, exp_avg_sq, slow)."""
+    b1, b2 = betas
+    v = exp_avg_sq * b2 + (1 - b2) * grad * grad
+    m = exp_avg * b1 + (1 - b1) * grad
+    n_sma, rect, plain = _radam_scalars(step, b1, b2)
+    p = param
+    if weight_decay != 0:
+        p = p + (-weight_decay * lr) * p
+    if n_sma > n_sma_threshold:
+        p = p + (-rect * lr) * (m / (v.sqrt() + eps))
+    else:
+        p = p + (-plain * lr) * m
+    if step % k == 0:
+        slow = slow + alpha * (p - slow)
+        p = slow
+    return p, m, v, slow

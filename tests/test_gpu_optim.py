@@ -186,3 +186,122 @@ def test_graphed_step_matches_eager(dev):
         ra = render_rays(a, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
         rb = render_rays(b, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
     assert (ra["rgb_fine"] - rb["rgb_fine"]).abs().max().item() < 2e-2
+
+
+# ---- a28: sgd / radam / ranger over the flat buffers (tests/make_golden_optim.py: the reference's own classes) ----------
+from tests.test_oracle_golden import OPT_CASES  # noqa: E402
+
+
+@pytest.mark.parametrize("name", list(OPT_CASES))
+def test_other_optimizers_kernel_vs_reference_golden(dev, name):
+    """Eight recorded steps of torch.optim.SGD / the reference's RAdam / Ranger through nrf_sgd_step / nrf_radam_step.
+    4e-7 absolute on 0.1-scale parameters per step (a few fp32 ulp; the updates are <= ~lr = 5e-4)."""
+    from nerf_pl_b200 import _lib
+    from nerf_pl_b200.ops import _p, _stream
+    z = np.load(os.path.join(GOLDEN, "optim.npz"))
+    kind, kw = OPT_CASES[name]
+    lr = float(z["lr"])
+    p = torch.from_numpy(z[f"{name}.p0"]).to(dev)
+    m, v, slow, buf = torch.zeros_like(p), torch.zeros_like(p), p.clone(), torch.zeros_like(p)
+    wd = kw.get("weight_decay", 0.0)
+    for t in range(z[f"{name}.grads"].shape[0]):
+        g = torch.from_numpy(z[f"{name}.grads"][t]).to(dev)
+        if kind == "sgd":
+            _lib.call("nrf_sgd_step", _p(p), _p(g), _p(buf), p.numel(), lr, kw["momentum"], wd, int(t == 0), _stream())
+        elif kind == "radam":
+            _lib.call("nrf_radam_step", _p(p), _p(g), _p(m), _p(v), None, p.numel(), lr, 0.9, 0.999, 1e-8, wd, t + 1, 0,
+                      5.0, int(kw.get("degenerated_to_sgd", True)), 0.0, 1, _stream())
+        else:
+            _lib.call("nrf_radam_step", _p(p), _p(g), _p(m), _p(v), _p(slow), p.numel(), lr, 0.95, 0.999, kw["eps"], wd,
+                      t + 1, 1, 5.0, 1, kw.get("alpha", 0.5), kw.get("k", 6), _stream())
+        want = torch.from_numpy(z[f"{name}.params"][t]).to(dev)
+        assert torch.allclose(p, want, rtol=0, atol=4e-7), (name, t, (p - want).abs().max().item())
+    gs = torch.from_numpy(np.abs(z[f"{name}.grads"]).max(0))
+    if kind != "sgd":
+        assert ((m.cpu() - torch.from_numpy(z[f"{name}.exp_avg"])).abs() <= 1e-6 * gs).all()
+        assert ((v.cpu() - torch.from_numpy(z[f"{name}.exp_avg_sq"])).abs() <= 1e-6 * gs * gs).all()
+    if kind == "ranger":
+        assert torch.allclose(slow.cpu(), torch.from_numpy(z[f"{name}.slow_buffer"]), rtol=0, atol=4e-7)
+    if name == "sgd_mom_wd":
+        assert ((buf.cpu() - torch.from_numpy(z[f"{name}.momentum_buffer"])).abs() <= 1e-5 * (gs + 1e-5)).all()
+    if name == "radam_nosgd":
+        pass  # covered above: parameters equal p0 through step 5
+
+
+def test_other_optimizers_errors_and_edges(dev):
+    from nerf_pl_b200 import _lib
+    from nerf_pl_b200.ops import _p, _stream
+    p = torch.zeros(4, device=dev)
+    _lib.call("nrf_sgd_step", None, None, None, 0, 1e-3, 0.0, 0.0, 1, _stream())           # empty: no-op
+    with pytest.raises(RuntimeError):
+        _lib.call("nrf_sgd_step", _p(p), _p(p), None, 4, 1e-3, 0.9, 0.0, 1, _stream())      # momentum without a buffer
+    with pytest.raises(RuntimeError):
+        _lib.call("nrf_radam_step", _p(p), _p(p), _p(p), _p(p), None, 4, 1e-3, 0.9, 0.999, 1e-8, 0.0, 0, 0, 5.0, 1, 0.0, 1,
+                  _stream())                                                                  # step counts from 1
+    with pytest.raises(RuntimeError):
+        _lib.call("nrf_radam_step", _p(p), _p(p), _p(p), _p(p), None, 4, 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, 1, 5.0, 1, 0.5, 6,
+                  _stream())                                                                  # ranger without slow buffer
+
+
+@pytest.mark.parametrize("name", ["sgd", "radam", "ranger"])
+def test_get_optimizer_flat_classes_follow_the_oracle(dev, name):
+    """get_optimizer(hparams, models) (utils/__init__.py:10-30) on the real two-model parameter set: seven steps with
+    synthetic gradients in the bucket against the oracle on a CPU copy; the operand re-pack follows the update; the
+    state dict round-trips."""
+    import types
+    from nerf_pl_b200.models.nerf import NeRF
+    from nerf_pl_b200.optim import get_optimizer
+    torch.manual_seed(4)
+    models = [NeRF().to(dev), NeRF().to(dev)]
+    hp = types.SimpleNamespace(optimizer=name, lr=5e-4, momentum=0.9, weight_decay=1e-5)
+    opt = get_optimizer(hp, models)
+    assert isinstance(opt, torch.optim.Optimizer)
+    ref = opt.flat_param.detach().cpu().clone()
+    n = ref.numel()
+    m, v, slow, buf = torch.zeros(n), torch.zeros(n), ref.clone(), None
+    g = torch.Generator().manual_seed(8)
+    before = models[0].packed_weights().clone()
+    for t in range(7):
+        gr = torch.randn(n, generator=g) * 1e-2
+        opt.zero_grad()
+        opt.bucket.flat.copy_(gr.to(dev))
+        opt.step()
+        if name == "sgd":
+            ref, buf = O.sgd_step(ref, gr, buf, 5e-4, 0.9, 1e-5)
+        elif name == "radam":
+            ref, m, v = O.radam_step(ref, gr, m, v, t + 1, 5e-4, eps=1e-8, weight_decay=1e-5)
+        else:
+            ref, m, v, slow = O.ranger_step(ref, gr, m, v, slow, t + 1, 5e-4, eps=1e-8, weight_decay=1e-5)
+        assert torch.allclose(opt.flat_param.cpu(), ref, rtol=0, atol=1e-6), (t, (opt.flat_param.cpu() - ref).abs().max())
+    off = 0
+    for p in opt.bucket.params:                         # parameters still alias the flat buffer
+        assert p.data_ptr() == opt.flat_param.data_ptr() + 4 * off
+        off += p.numel()
+    assert not torch.equal(before, models[0].packed_weights())
+    sd = opt.state_dict()
+    assert sd["steps"] == 7
+    opt2 = get_optimizer(hp, [NeRF().to(dev), NeRF().to(dev)])
+    opt2.load_state_dict(sd)
+    assert torch.equal(opt2.flat_param, opt.flat_param) and opt2.steps == 7
+    with pytest.raises(ValueError):
+        get_optimizer(types.SimpleNamespace(optimizer="lamb", lr=1e-3), models)
+
+
+def test_load_ckpt_into_flat_parameters_repacks(dev, tmp_path):
+    """load_ckpt (utils/__init__.py:72-76) copies in place: parameters re-homed by a fused optimizer stay views of the
+    flat buffer and the bf16 operand images are re-packed on the next use."""
+    from nerf_pl_b200 import ckpt
+    from nerf_pl_b200.models.nerf import NeRF
+    from nerf_pl_b200.optim import FusedAdam
+    torch.manual_seed(6)
+    src = {"nerf_coarse": NeRF(), "nerf_fine": NeRF()}
+    path = str(tmp_path / "epoch=3.ckpt")
+    ckpt.save_ckpt(path, src)
+    models = [NeRF().to(dev), NeRF().to(dev)]
+    opt = FusedAdam(models)
+    before = models[1].packed_weights().clone()
+    ckpt.load_ckpt(models[0], path, model_name="nerf_coarse")
+    ckpt.load_ckpt(models[1], path, model_name="nerf_fine")
+    want = torch.cat([p.detach().reshape(-1) for m in src.values() for p in m.parameters()])
+    assert torch.equal(opt.flat_param.cpu(), want)
+    assert not torch.equal(before, models[1].packed_weights())

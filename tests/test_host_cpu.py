@@ -136,3 +136,29 @@ def test_install_as_models_aliases():
         for k in [k for k in sys.modules if k == "models" or k.startswith("models.") or k == "torchsearchsorted"]:
             del sys.modules[k]
         sys.modules.update(saved)
+
+
+def test_checkpoint_layout_roundtrip(tmp_path):
+    """utils/__init__.py:55-76: Lightning-layout and weights-only checkpoints, model_name filter, prefixes_to_ignore; the
+    key / shape contract is the reference NeRF's (golden render_small.npz was produced through load_state_dict of it)."""
+    from nerf_pl_b200 import ckpt
+    from nerf_pl_b200.models.nerf import NeRF
+    torch.manual_seed(0)
+    a, b = NeRF(), NeRF()
+    keys = list(a.state_dict())
+    assert len(keys) == 24 and keys[0] == "xyz_encoding_1.0.weight" and a.state_dict()["xyz_encoding_5.0.weight"].shape == (256, 319)
+    for lightning in (True, False):
+        path = str(tmp_path / f"ck_{lightning}.ckpt")
+        ckpt.save_ckpt(path, {"nerf_coarse": a, "nerf_fine": b}, lightning=lightning, epoch=3)
+        raw = torch.load(path)
+        assert ("state_dict" in raw) == lightning
+        c, d = NeRF(), NeRF()
+        ckpt.load_ckpt(c, path, model_name="nerf_coarse")
+        ckpt.load_ckpt(d, path, model_name="nerf_fine")
+        for k in keys:
+            assert torch.equal(c.state_dict()[k], a.state_dict()[k]) and torch.equal(d.state_dict()[k], b.state_dict()[k])
+    e = NeRF()
+    before = e.rgb[0].weight.detach().clone()
+    ckpt.load_ckpt(e, path, model_name="nerf_coarse", prefixes_to_ignore=["rgb"])
+    assert torch.equal(e.rgb[0].weight, before) and torch.equal(e.sigma.weight, a.sigma.weight)
+    assert ckpt.extract_model_state_dict(path, "nerf_none") == {}

@@ -302,3 +302,48 @@ def test_oracle_shadow_image_run_vs_reference(tag, mode):
     for g, k in ((rc.grad, "g_range_cam"), (rl.grad, "g_range_light")):
         ref = T(f"{tag}/{k}")
         assert torch.allclose(g, ref, rtol=1e-4, atol=1e-5 * float(ref.abs().max())), k
+
+
+# ---- sgd / radam / ranger (utils/__init__.py:14-27, utils/optimizers.py), tests/make_golden_optim.py ---------------------
+OPT_CASES = {
+    "sgd_plain": ("sgd", dict(momentum=0.0, weight_decay=0.0)),
+    "sgd_mom_wd": ("sgd", dict(momentum=0.9, weight_decay=1e-4)),
+    "radam_wd0": ("radam", dict(weight_decay=0.0)),
+    "radam_wd": ("radam", dict(weight_decay=1e-4)),
+    "radam_nosgd": ("radam", dict(weight_decay=1e-4, degenerated_to_sgd=False)),
+    "ranger_wd0": ("ranger", dict(eps=1e-8, weight_decay=0.0)),
+    "ranger_wd": ("ranger", dict(eps=1e-8, weight_decay=1e-4)),
+    "ranger_k2": ("ranger", dict(eps=1e-8, alpha=0.3, k=2, weight_decay=0.0)),
+}
+
+
+@pytest.mark.parametrize("name", list(OPT_CASES))
+def test_oracle_optimizers_vs_reference_golden(name):
+    """oracle.sgd_step / radam_step / ranger_step against eight recorded steps of torch.optim.SGD and of the reference's
+    own RAdam / Ranger classes.  Tolerance: 1e-6 of the parameter scale per step (fp32 evaluation order)."""
+    z = np.load(os.path.join(G, "optim.npz"))
+    kind, kw = OPT_CASES[name]
+    lr = float(z["lr"])
+    p = torch.from_numpy(z[f"{name}.p0"])
+    n = p.numel()
+    m, v, slow, buf = torch.zeros(n), torch.zeros(n), p.clone(), None
+    for t in range(z[f"{name}.grads"].shape[0]):
+        g = torch.from_numpy(z[f"{name}.grads"][t])
+        if kind == "sgd":
+            p, buf = O.sgd_step(p, g, buf, lr, **kw)
+        elif kind == "radam":
+            p, m, v = O.radam_step(p, g, m, v, t + 1, lr, **kw)
+        else:
+            p, m, v, slow = O.ranger_step(p, g, m, v, slow, t + 1, lr, **kw)
+        ref = torch.from_numpy(z[f"{name}.params"][t])
+        assert torch.allclose(p, ref, rtol=1e-5, atol=1e-7), (name, t, float((p - ref).abs().max()))
+    gs = torch.from_numpy(np.abs(z[f"{name}.grads"]).max(0))       # per-element gradient scale (six decades)
+    if kind != "sgd":
+        assert bool(((m - torch.from_numpy(z[f"{name}.exp_avg"])).abs() <= 1e-6 * gs).all())
+        assert bool(((v - torch.from_numpy(z[f"{name}.exp_avg_sq"])).abs() <= 1e-6 * gs * gs).all())
+    if kind == "ranger":
+        assert torch.allclose(slow, torch.from_numpy(z[f"{name}.slow_buffer"]), rtol=1e-5, atol=1e-7)
+    if name == "sgd_mom_wd":
+        assert bool(((buf - torch.from_numpy(z[f"{name}.momentum_buffer"])).abs() <= 1e-5 * (gs + 1e-5)).all())
+    if name == "radam_nosgd":      # no parameter change while N_sma < 5 (steps 1-5)
+        assert np.array_equal(z[f"{name}.params"][4], z[f"{name}.p0"])
