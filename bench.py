@@ -8,6 +8,7 @@ on N B200s, BASELINE.json configs[1]: batch 4096 rays per GPU, bf16 tensor-core 
 One JSON line on stdout (rank 0).  Keys follow the driver contract; see DESIGN.md §5."""
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -64,14 +65,52 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock, power and throttle reasons sampled DURING the timed region: NVML every 2 ms from a thread (a 40 ms
+    timed region still gets ~20 samples), `nvidia-smi -lms 100` when the NVML binding is missing."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
 
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, index, uuid=None):
+        self.index, self.rows, self.proc, self.nv, self.h = index, [], None, None, None
+        self.sm, self.pw, self.mx, self.reasons, self.stop_flag, self.thread = [], [], 0.0, set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            if uuid:
+                try:
+                    h = pynvml.nvmlDeviceGetHandleByUUID(uuid if isinstance(uuid, bytes) else str(uuid).encode())
+                except Exception:
+                    h = None
+            self.h = h if h is not None else pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nv = pynvml
+        except Exception:
+            self.nv = None
+
+    def _nvml_loop(self):
+        nv, h = self.nv, self.h
+        reasons_fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while not self.stop_flag:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                self.pw.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
+                r = int(reasons_fn(h))
+                for bit, name in self.BITS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def start(self):
+        self.sm, self.pw, self.reasons, self.rows, self.stop_flag = [], [], set(), [], False
+        if self.nv is not None:
+            self.thread = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.thread.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -85,6 +124,14 @@ class ClockSampler:
             self.rows.append(line.strip())
 
     def stop(self):
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join()
+            self.thread = None
+            sm, pw = sorted(self.sm), sorted(self.pw)
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_min_mhz": sm[0] if sm else None,
+                    "sm_max_mhz": self.mx or None, "power_w": pw[len(pw) // 2] if pw else None,
+                    "reasons": sorted(self.reasons), "samples": len(sm), "source": "nvml, 2 ms period"}
         if self.proc is not None:
             self.proc.terminate()
         sm, mx, reasons = [], 0.0, set()
@@ -101,21 +148,25 @@ class ClockSampler:
                 pass
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
-def cpu_reference_rate(n_rays, reps, threads=None):
-    """The reference algorithm (oracle port of models/rendering.py) fwd+bwd on the host cores."""
+def cpu_reference_rate(n_rays, reps, threads=None, device="cpu"):
+    """The reference algorithm (oracle port of models/rendering.py) fwd+bwd on the host cores; with device="cuda" the
+    same eager-PyTorch fp32 program on the GPU (SURVEY §8d's "before" number: what the reference's own torch path does
+    on this B200, reported inside cpu_baseline, never the thing shipped)."""
     import torch
     from oracle import nerf_oracle as O
     cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
-    params = [O.init_mlp_params(generator=torch.Generator().manual_seed(s)) for s in (0, 1)]
+    on_gpu = device != "cpu"
+    params = [{k: v.to(device) for k, v in O.init_mlp_params(generator=torch.Generator().manual_seed(s)).items()}
+              for s in (0, 1)]
     for p in params:
         for v in p.values():
             v.requires_grad_()
-    rays = O.blender_rays(n_rays, seed=1)
-    noise = O.make_noise(n_rays, NC, NF, seed=2)
+    rays = O.blender_rays(n_rays, seed=1).to(device)
+    noise = {k: v.to(device) for k, v in O.make_noise(n_rays, NC, NF, seed=2).items()}
     opt = torch.optim.Adam([v for p in params for v in p.values()], lr=5e-4, eps=1e-8)   # utils/__init__.py:17-19
     times = []
     for i in range(reps + 1):
@@ -126,6 +177,9 @@ def cpu_reference_rate(n_rays, reps, threads=None):
         loss = ((out["rgb_coarse"] - 0.5) ** 2).mean() + ((out["rgb_fine"] - 0.5) ** 2).mean()
         loss.backward()
         opt.step()
+        if on_gpu:
+            loss.item()
+            torch.cuda.synchronize()
         if i > 0:      # first call is warm-up
             times.append(time.perf_counter() - t0)
     times.sort()
@@ -223,7 +277,11 @@ def run_gpu(args):
         step(rays_dev, rgbs_dev)
     sync_all()
 
-    sampler = ClockSampler(local_rank)
+    try:
+        uuid = "GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid)
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(local_rank, uuid)
     if rank == 0:
         sampler.start()
     # ---- eager pass: per-kernel CUDA-event pairs for the roofline, launch count -----------------------------
@@ -254,22 +312,53 @@ def run_gpu(args):
     sync_all()
     ms = sum(a.elapsed_time(b) for a, b in ev) / K
     # ---- end to end: pinned host -> device copies and the loss read-back inside the timed region ------
-    t_e2e = 0.0
+    # (a) blocking: every step waits for its own loss before the next is issued (the GPU idles while Python turns around)
+    t_sync = 0.0
     for i in range(K):
         flush.zero_()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         loss = graphed(rays_host, rgbs_host)          # H2D of rays + targets, then one graph launch
         loss_host = loss.item()                       # device -> host read of the step's result
-        t_e2e += time.perf_counter() - t0
+        t_sync += time.perf_counter() - t0
     sync_all()
-    ms_e2e = t_e2e / K * 1e3
+    ms_e2e_sync = t_sync / K * 1e3
+    # (b) pipelined (GraphedStep.submit, two steps in flight): each step still uploads its rays / targets from pinned
+    # host memory and its loss is still read back on the host, one step late, all inside the timed region (the last
+    # step's read-back drains the pipeline before the clock stops).  No explicit L2 flush here (it would sit inside the
+    # wall-clock region): a step streams ~16 GB through the 126 MB L2 by itself.
+    sync_all()
+    t0 = time.perf_counter()
+    pending, losses_host = None, []
+    for i in range(K):
+        nxt = graphed.submit(rays_host, rgbs_host)
+        if pending is not None:
+            losses_host.append(float(pending.result()))
+        pending = nxt
+    losses_host.append(float(pending.result()))
+    ms_e2e = (time.perf_counter() - t0) / K * 1e3
+    sync_all()
+    assert len(losses_host) == K and all(math.isfinite(v) for v in losses_host), losses_host
     clocks = sampler.stop() if rank == 0 else None
+    # ---- sustained regime: SUSTAIN back-to-back replays (~1 s) under one event pair.  A 10-step run is a 40 ms burst at
+    # the maximum SM clock; a long run settles at the board's power cap and a lower clock.  Reported beside `value`.
+    SUSTAIN = 250
+    sync_all()
+    if rank == 0:
+        sampler.start()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for i in range(SUSTAIN):
+        graphed(*graphed.static_in)
+    s1.record()
+    sync_all()
+    ms_sustained = s0.elapsed_time(s1) / SUSTAIN
+    clocks_sustained = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([ms, ms_e2e, ms_eager], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, ms_e2e, ms_eager, ms_e2e_sync, ms_sustained], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e, ms_eager = float(t[0]), float(t[1]), float(t[2])
+    ms, ms_e2e, ms_eager, ms_e2e_sync, ms_sustained = (float(v) for v in t)
 
     # ---- roofline: every tensor-core MLP kernel of the step, timed live over the timed region above ------------
     roof = None
@@ -371,14 +460,36 @@ def run_gpu(args):
                            "step_tensor_roofline_frac": rays_per_s * FLOP_PER_RAY_TRAIN / world / (peaks["bf16_tflops"] * 1e12)},
                 "clocks": clocks, "gpu_launches": launches,
                 "e2e": {"value": world * B / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
-                        "api": "nerf_pl_b200.graph.GraphedStep(step)(rays_host, rgbs_host): the whole step as one CUDA-graph launch",
+                        "api": "nerf_pl_b200.graph.GraphedStep(step).submit(rays_host, rgbs_host) -> handle.result(): the whole "
+                               "step as one CUDA-graph launch, two steps in flight, every step's inputs copied from pinned "
+                               "host memory and every step's loss read back on the host (one step late)",
+                        "blocking": {"value": world * B / (ms_e2e_sync * 1e-3), "ms_per_step": ms_e2e_sync,
+                                     "api": "loss = GraphedStep(step)(rays_host, rgbs_host).item() every step"},
                         "h2d_bytes_per_step": B * 8 * 4 + B * 3 * 4, "d2h_bytes_per_step": 4},
+                "sustained": {"value": world * B / (ms_sustained * 1e-3), "unit": "rays/s", "ms_per_step": ms_sustained,
+                              "steps": SUSTAIN, "clocks": clocks_sustained,
+                              "note": "back-to-back graph replays, no L2 flush (a step streams ~16 GB), one event pair"},
                 "roofline": roof, "side_rows": side_rows}
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, med = cpu_reference_rate(1024, 5)
             line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
                                     "sample": f"1024 rays per call (bounded sample of the 4096-ray batch), median of 5, "
                                               f"{med:.2f} s per call"}
+            # the same eager fp32 PyTorch program on this GPU (the reference's own execution model), whole 4096-ray batch
+            same_gpu = {}
+            for tag, tf32 in (("fp32", False), ("tf32", True)):
+                torch.backends.cuda.matmul.allow_tf32 = tf32
+                torch.backends.cudnn.allow_tf32 = tf32
+                try:
+                    r, _, m = cpu_reference_rate(B, 5, device="cuda")
+                    same_gpu[tag] = {"value": r, "unit": "rays/s", "ms_per_step": m * 1e3}
+                except Exception as e:      # noqa: BLE001  (a baseline must never take the bench line down)
+                    same_gpu[tag] = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+            torch.backends.cuda.matmul.allow_tf32 = False
+            torch.backends.cudnn.allow_tf32 = False
+            same_gpu["what"] = (f"oracle port (eager PyTorch, ~300 launches per step, fp32 activations in HBM) on the same "
+                                f"B200, {B} rays per step, fwd+bwd+Adam, wall clock with a sync per step, median of 5")
+            line["cpu_baseline"]["torch_cuda_same_gpu"] = same_gpu
         print(json.dumps(line), flush=True)
     graphed.close()          # before the process group goes away: the graph holds a captured NCCL all-reduce
     if world > 1:

@@ -40,6 +40,8 @@ class GraphedStep:
         with torch.cuda.graph(self.graph):
             self.static_out = fn(*self.static_in)
         self.replays = 0
+        self._ring = None
+        self._inflight = []
 
     def __call__(self, *inputs):
         if len(inputs) != len(self.static_in):
@@ -56,6 +58,30 @@ class GraphedStep:
         self.replays += 1
         return self.static_out
 
+    def submit(self, *inputs, depth=2):
+        """Pipelined form of __call__ for training loops that read the loss one step late: queues the pinned-host ->
+        device copies of this step's inputs, the graph launch and an asynchronous read-back of the outputs into a
+        pinned slot, and returns at once with a handle; `handle.result()` waits for THAT step only and returns host
+        copies of its outputs.  With `depth` steps in flight the GPU never idles while Python turns around after a
+        read-back (the ~0.2 ms per step that the blocking form loses).  The caller must not overwrite a host input
+        buffer before the step that reads it has been collected."""
+        if self._ring is None or len(self._ring) != depth:
+            outs = self.static_out if isinstance(self.static_out, (tuple, list)) else (self.static_out,)
+            self._ring = [([torch.empty(o.shape, dtype=o.dtype, pin_memory=True) for o in outs], torch.cuda.Event())
+                          for _ in range(depth)]
+            self._inflight = [False] * depth
+        slot = self.replays % depth
+        host_out, done = self._ring[slot]
+        if self._inflight[slot]:
+            done.synchronize()          # the slot's previous result has not been collected: do not overwrite in flight
+        self(*inputs)
+        outs = self.static_out if isinstance(self.static_out, (tuple, list)) else (self.static_out,)
+        for h, o in zip(host_out, outs):
+            h.copy_(o.detach(), non_blocking=True)
+        done.record()
+        self._inflight[slot] = True
+        return _Pending(self, slot, isinstance(self.static_out, (tuple, list)))
+
     def close(self):
         """Release the captured graph and its memory pool.  Call before torch.distributed.destroy_process_group():
         NCCL waits for graphs that captured its collectives to be destroyed."""
@@ -64,3 +90,17 @@ class GraphedStep:
         if self.graph is not None:
             self.graph.reset()
             self.graph = None
+
+
+class _Pending:
+    """Handle returned by GraphedStep.submit."""
+
+    def __init__(self, owner, slot, many):
+        self.owner, self.slot, self.many = owner, slot, many
+
+    def result(self):
+        host_out, done = self.owner._ring[self.slot]
+        done.synchronize()
+        self.owner._inflight[self.slot] = False
+        vals = [h.clone() for h in host_out]
+        return tuple(vals) if self.many else vals[0]

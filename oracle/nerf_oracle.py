@@ -111,7 +111,7 @@ def stratified_z(rays: Tensor, n_samples: int, use_disp: bool, perturb: float,
                  u_perturb: Optional[Tensor]) -> Tensor:
     """Coarse depths (models/rendering.py:216-232)."""
     near, far = rays[:, 6:7], rays[:, 7:8]
-    t = torch.linspace(0, 1, n_samples)
+    t = torch.linspace(0, 1, n_samples, device=rays.device)
     if use_disp:
         z = 1 / (1 / near * (1 - t) + 1 / far * t)
     else:

@@ -305,3 +305,38 @@ def test_load_ckpt_into_flat_parameters_repacks(dev, tmp_path):
     want = torch.cat([p.detach().reshape(-1) for m in src.values() for p in m.parameters()])
     assert torch.equal(opt.flat_param.cpu(), want)
     assert not torch.equal(before, models[1].packed_weights())
+
+
+def test_graphed_step_submit_pipeline(dev):
+    """GraphedStep.submit: inputs from pinned host memory, results read back per step through the handle, in order, with
+    two (and three) steps in flight; an uncollected slot is not overwritten while in flight."""
+    from nerf_pl_b200.graph import GraphedStep
+    w = torch.arange(1.0, 1025.0, device=dev)
+    state = torch.zeros((), device=dev)
+
+    def fn(x):
+        state.add_(1.0)                                   # device-side state advances once per replay
+        return (x * w).sum() + state, x.max()
+
+    g = GraphedStep(fn, (torch.zeros(1024, device=dev),), warmup=1)
+    base = float(state.item())                            # warm-up + capture executions
+    hosts = [torch.full((1024,), float(i + 1)).pin_memory() for i in range(6)]
+    for depth in (2, 3):
+        start = g.replays
+        handles = [g.submit(h, depth=depth) for h in hosts[:depth]]
+        got = [h.result() for h in handles]
+        for i, (a, b) in enumerate(got):
+            want = (i + 1) * float(w.sum().item()) + base + start + i + 1
+            assert abs(float(a) - want) <= 1e-6 * want and float(b) == i + 1
+        base_after = float(state.item())
+        assert base_after == base + start + depth
+    # lagged collection, as a training loop does it
+    pend, seen = None, []
+    for h in hosts:
+        nxt = g.submit(h)
+        if pend is not None:
+            seen.append(float(pend.result()[1]))
+        pend = nxt
+    seen.append(float(pend.result()[1]))
+    assert seen == [1.0, 2.0, 3.0, 4.0, 5.0, 6.0]
+    g.close()
