@@ -64,6 +64,15 @@ def load_peaks():
         return {"bf16_tflops": 1400.0, "bf16_burst": 1590.0, "hbm_gbs": 6650.0, "src": "fallback"}
 
 
+_RESULT_OUT = None
+
+
+def emit(line):
+    out = _RESULT_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 class ClockSampler:
     """SM clock, power and throttle reasons sampled DURING the timed region: NVML every 2 ms from a thread (a 40 ms
     timed region still gets ~20 samples), `nvidia-smi -lms 100` when the NVML binding is missing."""
@@ -202,7 +211,7 @@ def run_reference(args):
             "cpu_baseline": {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
                              "sample": f"{n} rays per step (bounded sample of the 4096-ray batch), median of {reps}"},
             "e2e": {"value": rate, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_gpu(args):
@@ -490,7 +499,7 @@ def run_gpu(args):
             same_gpu["what"] = (f"oracle port (eager PyTorch, ~300 launches per step, fp32 activations in HBM) on the same "
                                 f"B200, {B} rays per step, fwd+bwd+Adam, wall clock with a sync per step, median of 5")
             line["cpu_baseline"]["torch_cuda_same_gpu"] = same_gpu
-        print(json.dumps(line), flush=True)
+        emit(line)
     graphed.close()          # before the process group goes away: the graph holds a captured NCCL all-reduce
     if world > 1:
         dist.barrier()
@@ -507,6 +516,11 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # exactly ONE line on stdout: libraries that print there (NCCL's version banner under NCCL_DEBUG) go to stderr
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
