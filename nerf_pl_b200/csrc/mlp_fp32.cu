@@ -29,10 +29,12 @@ struct GemmOp {
   int64_t r_per_split;
 };
 
+// Register-prefetched, double-buffered SIMT GEMM: the next K tile's global loads are issued before the FFMAs of the
+// current one, index arithmetic (row offsets, the broadcast divisors) is hoisted out of the K loop, one barrier per tile.
 template <bool A_RCONTIG, bool B_JCONTIG>
-__global__ void __launch_bounds__(256) gemm_fp32_kernel(const GemmOp op) {
-  __shared__ float As[BK][BM + PAD];
-  __shared__ float Bs[BK][BN + PAD];
+__global__ void __launch_bounds__(256, 2) gemm_fp32_kernel(const GemmOp op) {
+  __shared__ float As[2][BK][BM + PAD];
+  __shared__ float Bs[2][BK][BN + PAD];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int64_t i0 = (int64_t)blockIdx.y * BM, j0 = (int64_t)blockIdx.x * BN;
   const int64_t r_begin = (int64_t)blockIdx.z * op.r_per_split;
@@ -45,35 +47,65 @@ __global__ void __launch_bounds__(256) gemm_fp32_kernel(const GemmOp op) {
   float asum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const bool do_colsum = op.a_colsum != nullptr && blockIdx.x == 0 && tx == 0;
 
+  // element e of this thread's 8 A loads sits at (i, r) = A_RCONTIG ? ((tid>>4) + 16 e, tid & 15) : (tid & 127, (tid>>7) + 2 e)
+  // and of its 8 B loads at (r, j) = B_JCONTIG ? ((tid>>7) + 2 e, tid & 127) : (tid & 15, (tid>>4) + 16 e)
+  const int a_i0 = A_RCONTIG ? (tid >> 4) : (tid & 127), a_r0 = A_RCONTIG ? (tid & 15) : (tid >> 7);
+  const int b_j0 = B_JCONTIG ? (tid & 127) : (tid >> 4), b_r0 = B_JCONTIG ? (tid >> 7) : (tid & 15);
+  const float* a_row[A_RCONTIG ? 8 : 1];          // row bases (null: out of range)
+  const float* b_col[B_JCONTIG ? 1 : 8];
+#pragma unroll
+  for (int e = 0; e < (A_RCONTIG ? 8 : 1); ++e) {
+    const int64_t gi = i0 + a_i0 + (A_RCONTIG ? 16 * e : 0);
+    a_row[e] = gi < op.I ? op.A + (gi / op.a_div_i) * op.sa_i : nullptr;
+  }
+#pragma unroll
+  for (int e = 0; e < (B_JCONTIG ? 1 : 8); ++e) {
+    const int64_t gj = j0 + b_j0 + (B_JCONTIG ? 0 : 16 * e);
+    b_col[e] = gj < op.J ? op.B + gj * op.sb_j : nullptr;
+  }
+  const unsigned b_div = (unsigned)op.b_div_r;
+  float pa[8], pb[8];
+
+  auto fetch = [&](int64_t r0) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int64_t gr = r0 + a_r0 + (A_RCONTIG ? 0 : 2 * e);
+      const float* row = a_row[A_RCONTIG ? e : 0];
+      pa[e] = (row != nullptr && gr < r_end) ? __ldg(row + gr * op.sa_r) : 0.f;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int64_t gr = r0 + b_r0 + (B_JCONTIG ? 2 * e : 0);
+      const float* col = b_col[B_JCONTIG ? 0 : e];
+      const int64_t br = b_div == 1u ? gr : (int64_t)((unsigned)gr / b_div);     // rows < 2^31 (grid.y limit)
+      pb[e] = (col != nullptr && gr < r_end) ? __ldg(col + br * op.sb_r) : 0.f;
+    }
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      if (A_RCONTIG) As[buf][a_r0][a_i0 + 16 * e] = pa[e]; else As[buf][a_r0 + 2 * e][a_i0] = pa[e];
+      if (B_JCONTIG) Bs[buf][b_r0 + 2 * e][b_j0] = pb[e]; else Bs[buf][b_r0][b_j0 + 16 * e] = pb[e];
+    }
+  };
+
+  int cur = 0;
+  if (r_begin < r_end) {
+    fetch(r_begin);
+    stash(0);
+  }
+  __syncthreads();
   for (int64_t r0 = r_begin; r0 < r_end; r0 += BK) {
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int idx = tid + e * 256;
-      int i, r;
-      if (A_RCONTIG) { i = idx >> 4; r = idx & 15; } else { r = idx >> 7; i = idx & 127; }
-      const int64_t gi = i0 + i, gr = r0 + r;
-      float v = 0.f;
-      if (gi < op.I && gr < r_end) v = op.A[(gi / op.a_div_i) * op.sa_i + (gr / op.a_div_r) * op.sa_r];
-      As[r][i] = v;
-    }
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int idx = tid + e * 256;
-      int j, r;
-      if (B_JCONTIG) { r = idx >> 7; j = idx & 127; } else { j = idx >> 4; r = idx & 15; }
-      const int64_t gj = j0 + j, gr = r0 + r;
-      float v = 0.f;
-      if (gj < op.J && gr < r_end) v = op.B[(gr / op.b_div_r) * op.sb_r + gj * op.sb_j];
-      Bs[r][j] = v;
-    }
-    __syncthreads();
+    const bool more = r0 + BK < r_end;
+    if (more) fetch(r0 + BK);
 #pragma unroll
     for (int kk = 0; kk < BK; ++kk) {
       float a[8], b[8];
-      *reinterpret_cast<float4*>(&a[0]) = *reinterpret_cast<const float4*>(&As[kk][ty * 8]);
-      *reinterpret_cast<float4*>(&a[4]) = *reinterpret_cast<const float4*>(&As[kk][ty * 8 + 4]);
-      *reinterpret_cast<float4*>(&b[0]) = *reinterpret_cast<const float4*>(&Bs[kk][tx * 8]);
-      *reinterpret_cast<float4*>(&b[4]) = *reinterpret_cast<const float4*>(&Bs[kk][tx * 8 + 4]);
+      *reinterpret_cast<float4*>(&a[0]) = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 8]);
+      *reinterpret_cast<float4*>(&a[4]) = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 8 + 4]);
+      // columns tx*4 .. +3 and 64 + tx*4 .. +3: a quarter warp reads 128 contiguous bytes (no bank conflicts)
+      *reinterpret_cast<float4*>(&b[0]) = *reinterpret_cast<const float4*>(&Bs[cur][kk][tx * 4]);
+      *reinterpret_cast<float4*>(&b[4]) = *reinterpret_cast<const float4*>(&Bs[cur][kk][64 + tx * 4]);
 #pragma unroll
       for (int x = 0; x < 8; ++x)
 #pragma unroll
@@ -83,7 +115,9 @@ __global__ void __launch_bounds__(256) gemm_fp32_kernel(const GemmOp op) {
         for (int x = 0; x < 8; ++x) asum[x] += a[x];
       }
     }
+    if (more) stash(cur ^ 1);
     __syncthreads();
+    cur ^= 1;
   }
 
 #pragma unroll
@@ -93,7 +127,7 @@ __global__ void __launch_bounds__(256) gemm_fp32_kernel(const GemmOp op) {
     if (do_colsum) atomicAdd(op.a_colsum + gi, asum[x]);
 #pragma unroll
     for (int y = 0; y < 8; ++y) {
-      const int64_t gj = j0 + tx * 8 + y;
+      const int64_t gj = j0 + (y < 4 ? tx * 4 + y : 64 + tx * 4 + (y - 4));
       if (gj >= op.J) continue;
       float* c = op.C + gi * op.ldc + gj;
       if (op.atomic) {
