@@ -118,6 +118,7 @@ class RenderPass(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, rays, z, noise, cfg, *params):
+        ctx.set_materialize_grads(False)      # unused outputs (depth, opacity, disp) arrive as None, not as zero fills
         need_grad = any(ctx.needs_input_grad[4:])
         sigma, rgb_s, saved = forward_rays(cfg.spec, params, rays, z, cfg.sigma_only, need_grad, cfg.precision,
                                            cfg.xyz_freqs, cfg.dir_freqs, getattr(cfg, "packed", None))

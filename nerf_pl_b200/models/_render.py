@@ -68,16 +68,34 @@ def render_rays_impl(variant, models, embeddings, rays, N_samples, use_disp, per
     depth_only = variant == "depth"
     with_disp = variant in ("depth", "rgb_sm")
 
-    u = None
-    if perturb > 0:
-        u = inj["u_perturb"] if "u_perturb" in inj else torch.rand(N, N_samples, device=dev)
+    # Random tensors the caller did not inject: ONE uniform draw and ONE normal draw per call, sliced per use
+    # (the reference makes five separate draws: rendering.py:231, :178, :36, :41, :178).
+    S_fine = N_samples + N_importance
+    need_u = [("u_perturb", N_samples)] if perturb > 0 else []
+    if N_importance > 0 and "z_fine" not in inj:
+        need_u += [("u_fine", N_importance), ("jitter_fine", N_importance)]
+    need_n = [("noise_coarse", N_samples)] + ([("noise_fine", S_fine)] if N_importance > 0 else []) if noise_std != 0 else []
+    drawn = {}
+    for need, fn in ((need_u, torch.rand), (need_n, torch.randn)):
+        need = [(k, w) for k, w in need if k not in inj]
+        if need:
+            pad = lambda v: (v + 63) // 64 * 64               # every slice starts 256-byte aligned (vector loads)
+            flat = fn(sum(pad(N * w) for _, w in need), device=dev)
+            off = 0
+            for k, w in need:
+                drawn[k] = flat[off:off + N * w].view(N, w)
+                off += pad(N * w)
+
+    def rnd(key):
+        return inj[key] if key in inj else drawn[key]
+
+    u = rnd("u_perturb") if perturb > 0 else None
     z = ops.sample_coarse(rays, N_samples, use_disp, perturb, u)
 
     def run(model, z_vals, noise_key, sigma_only):
         S = z_vals.shape[1]
-        noise = inj[noise_key] if noise_key in inj else torch.randn(N, S, device=dev)
         cfg = _model_cfg(model, embeddings, sigma_only, white_back, noise_std)
-        return RenderPass.apply(rays, z_vals, noise if noise_std != 0 else None, cfg, *model.ordered_parameters())
+        return RenderPass.apply(rays, z_vals, rnd(noise_key) if noise_std != 0 else None, cfg, *model.ordered_parameters())
 
     rgb_c, depth_c, opac_c, disp_c, w_c = run(models[0], z, "noise_coarse", test_time or depth_only)
     if test_time:
@@ -95,9 +113,7 @@ def render_rays_impl(variant, models, embeddings, rays, N_samples, use_disp, per
         if "z_fine" in inj:
             z_fine = inj["z_fine"]
         else:
-            uf = inj["u_fine"] if "u_fine" in inj else torch.rand(N, N_importance, device=dev)
-            jf = inj["jitter_fine"] if "jitter_fine" in inj else torch.rand(N, N_importance, device=dev)
-            z_fine = ops.sample_pdf(rays, w_c, N_importance, uf, jf)
+            z_fine = ops.sample_pdf(rays, w_c, N_importance, rnd("u_fine"), rnd("jitter_fine"))
         z_all = ops.merge_sort(z, z_fine)
         rgb_f, depth_f, opac_f, disp_f, _ = run(models[1], z_all, "noise_fine", depth_only)
         if not depth_only:

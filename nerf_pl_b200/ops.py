@@ -104,11 +104,17 @@ def _check_params(spec, params):
 # Stand-alone operators
 # --------------------------------------------------------------------------------------------
 
+_T_STEPS = {}
+
+
 def sample_coarse(rays, n_samples, use_disp, perturb, u=None, t_steps=None):
     rays = _dev(rays, "rays")
     N = rays.shape[0]
     if t_steps is None:
-        t_steps = torch.linspace(0, 1, n_samples, device=rays.device)
+        key = (n_samples, rays.device)
+        if key not in _T_STEPS:                   # constant of the call: one linspace per (Nc, device), not per step
+            _T_STEPS[key] = torch.linspace(0, 1, n_samples, device=rays.device)
+        t_steps = _T_STEPS[key]
     t_steps = _dev(t_steps, "t_steps")
     if perturb > 0:
         u = _dev(u, "u")
