@@ -196,6 +196,23 @@ def cpu_reference_rate(n_rays, reps, threads=None, device="cpu"):
     return n_rays / med, cores, med
 
 
+def cpu_frame_call_seconds(n_rays):
+    """One test-time render_rays call (config 3 settings) of the oracle port on the host cores, median of 3."""
+    import torch
+    from oracle import nerf_oracle as O
+    params = [O.init_mlp_params(generator=torch.Generator().manual_seed(s)) for s in (0, 1)]
+    rays = O.blender_rays(n_rays, seed=1)
+    noise = O.make_noise(n_rays, NC, NF, seed=2, perturb=False)
+    ts = []
+    with torch.no_grad():
+        for _ in range(4):
+            t0 = time.perf_counter()
+            O.render_rays(params, rays, n_samples=NC, perturb=0.0, noise_std=0.0, n_importance=NF, white_back=True,
+                          test_time=True, noise=noise)
+            ts.append(time.perf_counter() - t0)
+    return sorted(ts[1:])[1]
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -456,6 +473,21 @@ def run_gpu(args):
                  "mse_800x800x3": {"ms": t_mse, "gbs": 640000 * 3 * 8 / (t_mse * 1e-3) / 1e9, "bytes": 640000 * 3 * 8},
                  "note": "20 MB and 15 MB working sets: launch-latency bound, far below the 6.5 TB/s copy bandwidth"}
 
+    # BASELINE.json's second headline figure: one 800x800 test-time frame (config 3: perturb=0, noise_std=0, white_back,
+    # 20 calls of 32768 rays, test_time=True) rendered by THIS rank alone with the stepped weights (per-GPU figure; the
+    # ray-sharded N-GPU frame is tools/frame_bench.py)
+    if args.precision == "bf16":
+        frame = gen_rays(c2w, 800, 800, 1111.0, 2.0, 6.0, device=dev)
+
+        def render_frame():
+            with torch.no_grad():
+                return [render_rays(models, emb, frame[i:i + 32768], NC, False, 0, 0, NF, 1024 * 32, True, True)["rgb_fine"]
+                        for i in range(0, frame.shape[0], 32768)]
+        t_frame = timed(render_frame, reps=3)
+        side_rows["frame_800x800"] = {"ms": t_frame, "rays_per_s": 640000 / (t_frame * 1e-3),
+                                      "tflops": 640000 * (NC * 982528 + (NC + NF) * 1186816) / (t_frame * 1e-3) / 1e12,
+                                      "what": "config 3 on one GPU: coarse sigma-only + fine full MLP, 64+64 samples"}
+
     if rank == 0:
         rays_per_s = world * B / (ms * 1e-3)
         line = {"metric": "train_rays_per_sec", "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": K,
@@ -484,6 +516,13 @@ def run_gpu(args):
             line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
                                     "sample": f"1024 rays per call (bounded sample of the 4096-ray batch), median of 5, "
                                               f"{med:.2f} s per call"}
+            try:        # config 3 on the host cores: one 4096-ray test-time call, extrapolated x156.25 to 640 000 rays
+                tf = cpu_frame_call_seconds(4096)
+                line["cpu_baseline"]["frame_800x800_extrapolated_ms"] = tf * 640000 / 4096 * 1e3
+                line["cpu_baseline"]["frame_sample"] = f"one 4096-ray test_time call ({tf:.2f} s, median of 3) x 156.25, extrapolated"
+            except Exception as e:      # noqa: BLE001
+                line["cpu_baseline"]["frame_800x800_extrapolated_ms"] = None
+                line["cpu_baseline"]["frame_sample"] = f"unavailable: {type(e).__name__}: {e}"[:200]
             # the same eager fp32 PyTorch program on this GPU (the reference's own execution model), whole 4096-ray batch
             same_gpu = {}
             for tag, tf32 in (("fp32", False), ("tf32", True)):
