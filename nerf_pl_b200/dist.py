@@ -64,3 +64,54 @@ def render_sharded(render_fn, rays, group=None, gather_dst=0):
         if rank == gather_dst:
             out[k] = torch.cat([bufs[r][: b - a] for r, (a, b) in enumerate(sizes)], 0)
     return out if rank == gather_dst else None
+
+
+class _GatherRows(torch.autograd.Function):
+    """all_gather of contiguous row shards with a gradient: forward returns the full (n_total, ...) tensor on every
+    rank; backward sums the ranks' gradients of the full tensor and hands each rank its own rows (a reduce-scatter,
+    written as all_reduce + slice: the tensors here are a 64 KB depth map)."""
+
+    @staticmethod
+    def forward(ctx, local, n_total, group):
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        sizes = [shard_bounds(n_total, r, world) for r in range(world)]
+        lo, hi = sizes[rank]
+        if local.shape[0] != hi - lo:
+            raise RuntimeError(f"rank {rank} holds {local.shape[0]} rows, its shard of {n_total} is {hi - lo}")
+        pad_to = max(b - a for a, b in sizes)
+        v = local.contiguous()
+        if v.shape[0] < pad_to:
+            v = torch.cat([v, v.new_zeros((pad_to - v.shape[0],) + tuple(v.shape[1:]))], 0)
+        bufs = [torch.empty_like(v) for _ in range(world)]
+        dist.all_gather(bufs, v, group=group)
+        ctx.group, ctx.span = group, (lo, hi)
+        return torch.cat([bufs[r][: b - a] for r, (a, b) in enumerate(sizes)], 0)
+
+    @staticmethod
+    def backward(ctx, g):
+        g = g.contiguous().clone()
+        dist.all_reduce(g, op=dist.ReduceOp.SUM, group=ctx.group)
+        lo, hi = ctx.span
+        return g[lo:hi], None, None
+
+
+def gather_rows(local, n_total, group=None):
+    """Differentiable all_gather of row shards cut by shard_bounds (identity without a process group)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local
+    return _GatherRows.apply(local, n_total, group)
+
+
+def render_light_sharded(render_fn, light_rays, group=None):
+    """Shadow-mapping variant on N ranks (option ii): the light-view depth map is a dependency shared by
+    every rank's camera rays.  Each rank renders only its contiguous slice of the light rays and the per-ray results
+    (depth_coarse / depth_fine / ...) are all-gathered WITH gradient, so `efficient_sm` sees the whole light map on every
+    rank and, when the light render carries gradients (train_efficient_sm.py grad_on_light), every rank's shadow loss
+    reaches the slice that produced each texel.  Together with the mean all-reduce of the parameter gradients this
+    equals the replicated computation (every rank rendering all light rays) averaged over ranks."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    n = light_rays.shape[0]
+    lo, hi = shard_bounds(n, rank, world)
+    local = render_fn(light_rays[lo:hi])
+    return {k: gather_rows(v, n, group) for k, v in local.items()}

@@ -10,7 +10,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from nerf_pl_b200.dist import GradBucket, render_sharded, shard_bounds
+from nerf_pl_b200.dist import GradBucket, gather_rows, render_light_sharded, render_sharded, shard_bounds
 
 
 def _free_port():
@@ -63,6 +63,27 @@ def _worker(rank, world, port, n_rays, out_dir):
                 assert torch.equal(got[k], ref[k]), k
         else:
             assert got is None
+        # light-map sharding with gradients: every rank's loss uses the WHOLE gathered map; the gradient that reaches a
+        # rank's slice is the sum of all ranks' gradients on those texels (= the replicated computation)
+        n_light = max(n_rays // 3, 1)
+        light = torch.randn(n_light, 8, generator=torch.Generator().manual_seed(11))
+        w = torch.nn.Parameter(torch.tensor([0.7, -1.3]))
+        llo, lhi = shard_bounds(n_light, rank, world)
+
+        def light_fn(r):
+            return {"depth_coarse": w[0] * r[:, 6] + w[1] * r[:, 7] ** 2}
+
+        full = render_light_sharded(light_fn, light)["depth_coarse"]
+        assert full.shape == (n_light,)
+        assert torch.allclose(full.detach(), light_fn(light)["depth_coarse"].detach())
+        probe = torch.randn(n_light, generator=torch.Generator().manual_seed(200 + rank))     # rank-specific use of the map
+        (full * probe).sum().backward()
+        total_probe = sum(torch.randn(n_light, generator=torch.Generator().manual_seed(200 + r)) for r in range(world))
+        wr = torch.tensor([0.7, -1.3], requires_grad=True)
+        part = (wr[0] * light[llo:lhi, 6] + wr[1] * light[llo:lhi, 7] ** 2)
+        (part * total_probe[llo:lhi]).sum().backward()
+        assert torch.allclose(w.grad, wr.grad, rtol=1e-5, atol=1e-6)
+        assert gather_rows(part.detach(), n_light).shape == (n_light,)
         open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     finally:
         dist.destroy_process_group()
