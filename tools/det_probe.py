@@ -1,3 +1,8 @@
+"""Does a test-time render depend on how the rays are batched?  Renders 65 536 rays whole, twice, shifted by 1000 rays,
+as the second half only and in chunks of 8192, and compares bit for bit.  Finding: opacity_coarse is bit-identical in every
+case; the fine keys differ between ANY two calls because the fork's sample_pdf draws fresh uniforms on every call, test
+time included (rendering.py:36-41) - inject u_fine / jitter_fine (tools/frame_bench.py, tests/test_gpu_edges.py) and the
+fine keys are bit-identical too.      python tools/det_probe.py"""
 import math, os, sys
 sys.path.insert(0, os.getcwd())
 import torch
