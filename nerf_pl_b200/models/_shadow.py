@@ -53,13 +53,49 @@ class ShadowTest(torch.autograd.Function):
         return (g_cam, g_light) + (None,) * 9
 
 
+_SMALL_CONST = {}
+
+
 def _f32(t, dev):
-    return torch.as_tensor(t, dtype=torch.float32).to(dev).contiguous()
+    """fp32 contiguous device tensor.  Small host-resident values (camera matrices, eye positions) are cached by value:
+    a pageable host -> device copy makes the host wait for everything already queued on the stream, which drains the
+    pipeline once per step for a dozen numbers."""
+    t = torch.as_tensor(t, dtype=torch.float32)
+    if t.is_cuda or t.numel() > 64:
+        return t.to(dev).contiguous()
+    key = (t.detach().contiguous().numpy().tobytes(), tuple(t.shape), str(dev))
+    hit = _SMALL_CONST.get(key)
+    if hit is None:
+        if len(_SMALL_CONST) > 256:
+            _SMALL_CONST.clear()
+        hit = _SMALL_CONST[key] = t.detach().to(dev).contiguous()
+    return hit
+
+
+_INV_CACHE = {}
+
+
+def _inverse3(M_src, dev):
+    """(M^-1, M) of a 3x3 camera matrix as contiguous fp32 device tensors (models/camera.py:126: torch.inverse).  A
+    host-resident matrix - what models.camera.Camera holds - is inverted on the host (LAPACK, as the reference run on
+    the CPU does) and cached by value: torch.inverse on the device costs a cuSOLVER call with a host sync per step for
+    nine numbers.  A device-resident matrix is inverted on the device."""
+    t = torch.as_tensor(M_src, dtype=torch.float32)
+    if t.is_cuda:
+        M = t.to(dev).contiguous()
+        return torch.inverse(M).contiguous(), M
+    key = (t.detach().contiguous().numpy().tobytes(), str(dev))
+    hit = _INV_CACHE.get(key)
+    if hit is None:
+        if len(_INV_CACHE) > 64:
+            _INV_CACHE.clear()
+        hit = _INV_CACHE[key] = (torch.inverse(t.detach()).contiguous().to(dev), t.detach().contiguous().to(dev))
+    return hit
 
 
 def _light_static(light_camera, dev):
-    M = _f32(light_camera.camera, dev)
-    return torch.inverse(M).contiguous(), M, _f32(light_camera.eye_pos, dev)
+    inv, M = _inverse3(light_camera.camera, dev)
+    return inv, M, _f32(light_camera.eye_pos, dev)
 
 
 def efficient_sm_impl(prefix, cam_pixels, light_pixels, cam_results, light_results, ppc, light_ppc, image_shape,

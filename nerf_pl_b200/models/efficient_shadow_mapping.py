@@ -9,7 +9,7 @@ import torch
 
 from .. import _lib
 from ..ops import _dev, _p, _stream
-from ._shadow import LightGather, ProjectToLight, ShadowMap, ShadowTest, _f32
+from ._shadow import LightGather, ProjectToLight, ShadowMap, ShadowTest, _f32, _inverse3
 
 EPSILON = 1e-5
 
@@ -51,8 +51,8 @@ def run_shadow_mapping(res, camera, light_cam, batched_mesh_range_cam, meshed_no
     n = mrc.shape[0]
     cam_M = _f32(camera.camera, dev).reshape(1, 3, 3).expand(n, 3, 3).contiguous()
     eye = _f32(camera.eye_pos, dev).reshape(1, 3).expand(n, 3).contiguous()
-    LM = _f32(light_cam.camera, dev)
-    static = (mrc[:, :3].detach().contiguous(), cam_M, eye, torch.inverse(LM).contiguous(), None,
+    LM_src = light_cam.camera
+    static = (mrc[:, :3].detach().contiguous(), cam_M, eye, _inverse3(LM_src, dev)[0], None,
               _f32(light_cam.eye_pos, dev), None)
     return ShadowTest.apply(mrc[:, 3], meshed_normed_light_cam[:, 3], static, res, mode, delta, epsilon, new_min,
                             new_max, sigmoid, 0.0)
@@ -68,9 +68,9 @@ def get_diff_projections(pixels, w_cam, from_camera, to_camera, device='cpu'):
     """K (n,3) = [ul, vl, wl]: pixels (n,3) with normalised depth w_cam (n) of `from_camera` seen by `to_camera`
     (reference :65-83)."""
     dev = w_cam.device
-    LM = _f32(to_camera.camera, dev)
+    LM_src = to_camera.camera
     return ProjectToLight.apply(w_cam, _f32(pixels, dev), _f32(from_camera.camera, dev).reshape(1, 3, 3),
-                                _f32(from_camera.eye_pos, dev).reshape(1, 3), torch.inverse(LM).contiguous(),
+                                _f32(from_camera.eye_pos, dev).reshape(1, 3), _inverse3(LM_src, dev)[0],
                                 _f32(to_camera.eye_pos, dev), True)
 
 
@@ -78,9 +78,9 @@ def get_projections(camera, light_cam, batched_mesh_range_cam, device):
     """get_normed_w followed by get_diff_projections (reference :13-17), one kernel."""
     mrc = batched_mesh_range_cam
     dev = mrc.device
-    LM = _f32(light_cam.camera, dev)
+    LM_src = light_cam.camera
     return ProjectToLight.apply(mrc[:, 3], mrc[:, :3].detach().contiguous(), _f32(camera.camera, dev).reshape(1, 3, 3),
-                                _f32(camera.eye_pos, dev).reshape(1, 3), torch.inverse(LM).contiguous(),
+                                _f32(camera.eye_pos, dev).reshape(1, 3), _inverse3(LM_src, dev)[0],
                                 _f32(light_cam.eye_pos, dev), False)
 
 

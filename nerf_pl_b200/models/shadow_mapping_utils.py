@@ -8,7 +8,7 @@ import torch
 
 from .. import _lib
 from ..ops import _dev, _p, _stream
-from ._shadow import LightGather, ProjectToLight, ShadowMap, _f32
+from ._shadow import LightGather, ProjectToLight, ShadowMap, _f32, _inverse3
 
 _GRID = {}
 
@@ -69,10 +69,10 @@ def get_differentiable_projections(w_from_camera, res, from_camera, to_camera, d
     _check_square(res)
     dev = w_from_camera.device
     w, h = int(res[0]), int(res[1])
-    LM = _f32(to_camera.camera, dev)
+    LM_src = to_camera.camera
     K = ProjectToLight.apply(w_from_camera.reshape(-1), _pixel_grid(res, dev),
                              _f32(from_camera.camera, dev).reshape(1, 3, 3), _f32(from_camera.eye_pos, dev).reshape(1, 3),
-                             torch.inverse(LM).contiguous(), _f32(to_camera.eye_pos, dev), 1)
+                             _inverse3(LM_src, dev)[0], _f32(to_camera.eye_pos, dev), 1)
     return K.view(w, h, 3)
 
 
@@ -100,11 +100,11 @@ def run_shadow_mapping(res, camera, light_cam, range_cam, range_light, device, m
     dev = range_cam.device
     w, h = int(res[0]), int(res[1])
     grid = _pixel_grid(res, dev)
-    LM = _f32(light_cam.camera, dev)
-    w_light = _WMapping.apply(range_light.reshape(-1), grid, LM)
+    LM_src = light_cam.camera
+    w_light = _WMapping.apply(range_light.reshape(-1), grid, _inverse3(LM_src, dev)[1])
     # range -> w (no epsilon) -> projection, one kernel
     K = ProjectToLight.apply(range_cam.reshape(-1), grid, _f32(camera.camera, dev).reshape(1, 3, 3),
-                             _f32(camera.eye_pos, dev).reshape(1, 3), torch.inverse(LM).contiguous(),
+                             _f32(camera.eye_pos, dev).reshape(1, 3), _inverse3(LM_src, dev)[0],
                              _f32(light_cam.eye_pos, dev), 2)
     wlb = LightGather.apply(K.detach(), w_light, res)
     return ShadowMap.apply(K[:, 2], wlb, mode, delta, epsilon, new_min, new_max, sigmoid, True, True).view(w, h, 3)

@@ -112,6 +112,9 @@ light_pix = torch.cat([ij + 0.5, torch.ones(16384, 1)], 1)
 rays_c, rays_l = cam_rays(cam, ij[:4096]).to(dev), cam_rays(light, ij).to(dev)
 ppc = {"eye_pos": torch.as_tensor(cam.eye_pos, dtype=torch.float32).expand(4096, 3).contiguous(),
        "camera": torch.as_tensor(cam.camera, dtype=torch.float32).expand(4096, 3, 3).contiguous()}
+# the batch reaches the step on the device, as Lightning delivers it (train_efficient_sm.py:186-200)
+cam_pix, light_pix = cam_pix.to(dev), light_pix.to(dev)
+ppc = {k: v.to(dev) for k, v in ppc.items()}
 tgt5 = torch.rand(4096, 3, device=dev)
 sm_loss = loss_dict["mse"]()
 for lni, grad_light in ((0, False), (64, True)):
