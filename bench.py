@@ -473,6 +473,32 @@ def run_gpu(args):
                  "mse_800x800x3": {"ms": t_mse, "gbs": 640000 * 3 * 8 / (t_mse * 1e-3) / 1e9, "bytes": 640000 * 3 * 8},
                  "note": "20 MB and 15 MB working sets: launch-latency bound, far below the 6.5 TB/s copy bandwidth"}
 
+    # the HBM-bound kernels of the path itself, standalone at a test-time chunk (32768 rays; working sets 25-120 MB),
+    # against the algorithmic bytes of SURVEY 8d: sampling, inverse-CDF resampling, merge sort, compositing fwd / bwd
+    from nerf_pl_b200 import ops as _ops
+    Nr = 32768
+    r_big = gen_rays(c2w, 800, 800, 1111.0, 2.0, 6.0, device=dev)[:Nr].contiguous()
+    u64, j64 = torch.rand(Nr, NC, device=dev), torch.rand(Nr, NF, device=dev)
+    w_c = torch.rand(Nr, NC, device=dev)
+    S2 = NC + NF
+    z_c = _ops.sample_coarse(r_big, NC, False, 1.0, u64)
+    z_f = _ops.sample_pdf(r_big, w_c, NF, j64, j64)
+    z_a = _ops.merge_sort(z_c, z_f)
+    sig, col, nz = torch.randn(Nr, S2, device=dev), torch.rand(Nr, S2, 3, device=dev), torch.randn(Nr, S2, device=dev)
+    g3, g1 = torch.rand(Nr, 3, device=dev), torch.rand(Nr, device=dev)
+
+    def hbm_row(fn, nbytes):
+        t = timed(fn)
+        return {"ms": t, "gbs": nbytes / (t * 1e-3) / 1e9, "bytes": nbytes, "hbm_frac": nbytes / (t * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+    side_rows["path_kernels_32768_rays"] = {
+        "sample_coarse": hbm_row(lambda: _ops.sample_coarse(r_big, NC, False, 1.0, u64), Nr * (32 + 8 * NC)),
+        "sample_pdf": hbm_row(lambda: _ops.sample_pdf(r_big, w_c, NF, j64, j64), Nr * (4 * (NC - 2) + 12 * NF)),
+        "merge_sort": hbm_row(lambda: _ops.merge_sort(z_c, z_f), Nr * 8 * S2),
+        "composite_fwd": hbm_row(lambda: _ops.composite(sig, col, z_a, r_big, nz, 1.0, True), Nr * S2 * 28),
+        "composite_bwd": hbm_row(lambda: _ops.composite_bwd(sig, col, z_a, r_big, nz, 1.0, True, g3, g1, g1, None), Nr * S2 * 40),
+        "note": "algorithmic bytes per SURVEY 8d (fwd 28 B/sample incl. noise, bwd 40 B/sample); inside a training step "
+                "these five kernels together take ~50 us of 3.7 ms"}
+
     # BASELINE.json's second headline figure: one 800x800 test-time frame (config 3: perturb=0, noise_std=0, white_back,
     # 20 calls of 32768 rays, test_time=True) rendered by THIS rank alone with the stepped weights (per-GPU figure; the
     # ray-sharded N-GPU frame is tools/frame_bench.py)
