@@ -340,3 +340,58 @@ def test_graphed_step_submit_pipeline(dev):
     seen.append(float(pend.result()[1]))
     assert seen == [1.0, 2.0, 3.0, 4.0, 5.0, 6.0]
     g.close()
+
+
+def test_checkpoint_resume_continues_the_run(dev, tmp_path):
+    """Checkpoint / resume: three steps, save the models in the Lightning layout (ckpt.save_ckpt) and the
+    optimizer state (FusedAdam.state_dict through torch.save); the original run goes on for two more steps, and so does a
+    run rebuilt from the files alone (new modules, new optimizer).  The restored state is bit-identical and the two
+    continuations agree to 1e-6 on 99.9 % of the parameters and to 1e-4 everywhere (measured maxima 4.5e-8 .. 3.8e-6; their
+    only difference is the order of the fp32 atomics in two wgrad passes).  For scale: two UNINTERRUPTED five-step runs from the same initial weights differ by up to 3e-4 on a few
+    noise-dominated elements, because Adam normalises every gradient, however small."""
+    import copy
+    import nerf_pl_b200
+    from nerf_pl_b200 import ckpt
+    from nerf_pl_b200.losses import loss_dict
+    from nerf_pl_b200.models.nerf import Embedding, NeRF
+    from nerf_pl_b200.models.rendering import render_rays
+    from nerf_pl_b200.optim import FusedAdam
+    nerf_pl_b200.set_mlp_precision("bf16")
+    emb = [Embedding(3, 10), Embedding(3, 4)]
+    mse = loss_dict["mse"]()
+    n = 1024
+    rays = O.blender_rays(n, seed=4).to(dev)
+    tgt = torch.rand(n, 3, generator=torch.Generator().manual_seed(5)).to(dev)
+    noises = [{k: v.to(dev) for k, v in O.make_noise(n, 64, 64, seed=30 + i).items()} for i in range(5)]
+
+    def run(models, opt, steps):
+        for i in steps:
+            opt.zero_grad()
+            out = render_rays(models, emb, rays, 64, False, 1.0, 1.0, 64, 1024 * 32, True, _inject=noises[i])
+            mse(out, tgt).backward()
+            opt.step()
+
+    torch.manual_seed(8)
+    b = [NeRF().to(dev), NeRF().to(dev)]
+    opt_b = FusedAdam(b, lr=5e-4, weight_decay=1e-6)
+    run(b, opt_b, range(3))
+    ckpt.save_ckpt(str(tmp_path / "epoch=0.ckpt"), {"nerf_coarse": b[0], "nerf_fine": b[1]}, epoch=0)
+    torch.save(opt_b.state_dict(), str(tmp_path / "optim.pt"))
+
+    c = [NeRF().to(dev), NeRF().to(dev)]                    # "fresh process": new modules, new optimizer
+    opt_c = FusedAdam(c, lr=1e-3)                            # wrong hyper-parameters on purpose: the state restores them
+    ckpt.load_ckpt(c[0], str(tmp_path / "epoch=0.ckpt"), model_name="nerf_coarse")
+    ckpt.load_ckpt(c[1], str(tmp_path / "epoch=0.ckpt"), model_name="nerf_fine")
+    opt_c.load_state_dict(torch.load(str(tmp_path / "optim.pt")))
+    assert opt_c.steps == 3 and opt_c.param_groups[0]["lr"] == 5e-4 and opt_c.param_groups[0]["weight_decay"] == 1e-6
+    assert torch.equal(opt_c.flat_param, opt_b.flat_param)
+    assert torch.equal(opt_c.exp_avg, opt_b.exp_avg) and torch.equal(opt_c.exp_avg_sq, opt_b.exp_avg_sq)
+    run(b, opt_b, range(3, 5))
+    run(c, opt_c, range(3, 5))
+    assert opt_c.steps == 5
+    d = (opt_b.flat_param - opt_c.flat_param).abs()
+    assert float((d <= 1e-6).float().mean()) >= 0.999 and float(d.max()) <= 1e-4, float(d.max())
+    off = 0
+    for p in opt_c.bucket.params:                            # the new modules' parameters are views of the flat buffer
+        assert p.data_ptr() == opt_c.flat_param.data_ptr() + 4 * off
+        off += p.numel()
