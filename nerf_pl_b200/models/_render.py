@@ -62,6 +62,7 @@ def render_rays_impl(variant, models, embeddings, rays, N_samples, use_disp, per
     if not isinstance(rays, torch.Tensor) or rays.dim() != 2 or rays.shape[1] != 8:
         raise RuntimeError("rays must be a (N_rays, 8) tensor [o, d, near, far]")
     rays = ops._dev(rays.detach(), "rays")
+    ops.check_current_device(rays, "rays")
     inj = _inject or {}
     N = rays.shape[0]
     dev = rays.device

@@ -95,6 +95,7 @@ class NeRF(nn.Module):
             raise RuntimeError("nerf_pl_b200.NeRF needs CUDA tensors (no CPU path)")
         if xyz.dim() != 2 or xyz.shape[1] != 3 or (dirs is not None and dirs.shape != xyz.shape):
             raise RuntimeError("query expects xyz (B,3) and dirs (B,3)")
+        _ops.check_current_device(xyz, "xyz")
         B = xyz.shape[0]
         precision = _ops.get_mlp_precision()
         params = [p.detach() for p in self.ordered_parameters()]

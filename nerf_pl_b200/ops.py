@@ -43,6 +43,15 @@ def _p(t):
     return None if t is None else t.data_ptr()
 
 
+def check_current_device(t: torch.Tensor, name: str):
+    """The launchers use torch's CURRENT stream: a tensor on another GPU than the current device would be handed to a
+    kernel running on the wrong GPU.  One process per GPU with torch.cuda.set_device(local_rank) (or a
+    `with torch.cuda.device(...)` block) is the supported arrangement; anything else raises here."""
+    if t.is_cuda and t.device.index != torch.cuda.current_device():
+        raise RuntimeError(f"{name} lives on {t.device} but the current CUDA device is cuda:{torch.cuda.current_device()}: "
+                           "call torch.cuda.set_device() (one process per GPU) or wrap the call in torch.cuda.device(...)")
+
+
 # --------------------------------------------------------------------------------------------
 # MLP parameter plumbing
 # --------------------------------------------------------------------------------------------
