@@ -155,6 +155,82 @@ __global__ void merge_sort_kernel(const float* __restrict__ zc, const float* __r
   }
 }
 
+// Same result for the shape render_rays produces (rendering.py:257: the coarse depths are already ascending): bitonic
+// sort of the nf fine depths only, then a rank merge - a coarse element goes to i + #(fine < it), a fine element to
+// j + #(coarse <= it), two binary searches in shared memory.  The output is the same sorted multiset bit for bit.  Rays
+// whose coarse part is NOT ascending (callers outside render_rays) take the full network of merge_sort_kernel's body.
+__global__ void merge_sorted_kernel(const float* __restrict__ zc, const float* __restrict__ zf, int64_t n_rays,
+                                    int nc, int nf, int Pf, int P, float* __restrict__ z_out) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n = nc + nf;
+  const int per_warp = (nc + Pf > P ? nc + Pf : P) + n;
+  float* sc = smem + warp * per_warp;   // [nc] coarse, then [Pf] fine (also the [P] scratch of the fallback)
+  float* sf = sc + nc;
+  float* so = sc + (nc + Pf > P ? nc + Pf : P);   // [n] merged
+  for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerBlock + warp; ray < n_rays;
+       ray += (int64_t)gridDim.x * kWarpsPerBlock) {
+    bool ok = true;
+    for (int i = lane; i < nc; i += 32) sc[i] = __ldg(zc + ray * nc + i);
+    for (int i = lane; i < Pf; i += 32) sf[i] = i < nf ? __ldg(zf + ray * nf + i) : INFINITY;
+    __syncwarp();
+    for (int i = lane; i + 1 < nc; i += 32) ok = ok && (sc[i] <= sc[i + 1]);
+    ok = __all_sync(0xffffffffu, ok);
+    if (ok) {
+      for (int k = 2; k <= Pf; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          for (int t = lane; t < (Pf >> 1); t += 32) {
+            const int i = 2 * t - (t & (j - 1));
+            const int l = i + j;
+            const float a = sf[i], b = sf[l];
+            const bool asc = (i & k) == 0;
+            if ((a > b) == asc) { sf[i] = b; sf[l] = a; }
+          }
+          __syncwarp();
+        }
+      }
+      for (int i = lane; i < nc; i += 32) {
+        const float v = sc[i];
+        int lo = 0, hi = nf;                       // #(fine < v)
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (sf[mid] < v) lo = mid + 1; else hi = mid; }
+        so[i + lo] = v;
+      }
+      for (int j = lane; j < nf; j += 32) {
+        const float v = sf[j];
+        int lo = 0, hi = nc;                       // #(coarse <= v)
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (sc[mid] <= v) lo = mid + 1; else hi = mid; }
+        so[j + lo] = v;
+      }
+      __syncwarp();
+      for (int i = lane; i < n; i += 32) z_out[ray * n + i] = so[i];
+    } else {
+      float* s = sc;                               // full bitonic network over the concatenation, as merge_sort_kernel
+      __syncwarp();
+      for (int i = lane; i < P; i += 32) {
+        float v = INFINITY;
+        if (i < nc) v = __ldg(zc + ray * nc + i);
+        else if (i < n) v = __ldg(zf + ray * nf + (i - nc));
+        s[i] = v;
+      }
+      __syncwarp();
+      for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          for (int t = lane; t < (P >> 1); t += 32) {
+            const int i = 2 * t - (t & (j - 1));
+            const int l = i + j;
+            const float a = s[i], b = s[l];
+            const bool asc = (i & k) == 0;
+            if ((a > b) == asc) { s[i] = b; s[l] = a; }
+          }
+          __syncwarp();
+        }
+      }
+      for (int i = lane; i < n; i += 32) z_out[ray * n + i] = s[i];
+    }
+    __syncwarp();
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // a12  torchsearchsorted (searchsorted_cuda_kernel.cu:83-107): one thread per query.
 // ---------------------------------------------------------------------------------------------
@@ -227,6 +303,20 @@ extern "C" int nrf_merge_sort(const float* z_coarse, const float* z_fine, int64_
   NRF_REQUIRE((z_coarse || nc == 0) && (z_fine || nf == 0) && z_out, "nrf_merge_sort: null pointer");
   int P = 2;
   while (P < nc + nf) P <<= 1;
+  if (nc >= 2 && nf >= 1) {
+    int Pf = 2;
+    while (Pf < nf) Pf <<= 1;
+    const size_t per_warp = (size_t)((nc + Pf > P ? nc + Pf : P) + nc + nf);
+    const size_t smem2 = (size_t)kWarpsPerBlock * per_warp * sizeof(float);
+    if (smem2 <= 200 * 1024) {
+      if (smem2 > 48 * 1024)
+        NRF_CUDA(cudaFuncSetAttribute(merge_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      merge_sorted_kernel<<<grid_for(n_rays, kWarpsPerBlock), kWarpsPerBlock * 32, smem2, as_stream(stream)>>>(
+          z_coarse, z_fine, n_rays, nc, nf, Pf, P, z_out);
+      NRF_LAUNCH_CHECK();
+      return NRF_OK;
+    }
+  }
   const size_t smem = (size_t)kWarpsPerBlock * P * sizeof(float);
   if (smem > 48 * 1024)
     NRF_CUDA(cudaFuncSetAttribute(merge_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -114,6 +114,21 @@ def test_merge_sort_bit_exact(dev, nc, nf):
     assert bool((got[:, 1:] >= got[:, :-1]).all())
 
 
+@pytest.mark.parametrize("nc,nf", [(64, 64), (17, 37), (2, 1), (64, 200)])
+def test_merge_sort_unsorted_coarse_and_mixed_rays(dev, nc, nf):
+    """The rank-merge path needs ascending coarse depths (what render_rays produces); rays whose coarse part is not
+    ascending fall back to the full network inside the same launch.  Mixed batch: even rays sorted, odd rays shuffled."""
+    from nerf_pl_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    zc = torch.sort(torch.rand(257, nc, generator=g) * 4 + 2, -1)[0]
+    zc[1::2] = zc[1::2][:, torch.randperm(nc, generator=g)]
+    zf = torch.rand(257, nf, generator=g) * 4 + 2
+    zf[:, -1] = zc[:, 0]                              # a tie between the lists
+    ref = torch.sort(torch.cat([zc, zf], -1), -1)[0]
+    got = ops.merge_sort(zc.to(dev), zf.to(dev))
+    assert torch.equal(got.cpu(), ref)
+
+
 def _composite_case(N, S, seed, with_rgb=True, near=2.0, far=6.0):
     g = torch.Generator().manual_seed(seed)
     rays = _rays(N, near, far, unnorm=True)
