@@ -1,19 +1,29 @@
-"""Drop-in for metrics.py (reference :4-13): mse / psnr through the fused reduction kernel.  ssim (reference :15-20)
-wraps kornia, which this tier does not reimplement."""
+"""Image metrics with the reference's names and arguments (metrics.py:4-20).
+
+`mse` with the default 'mean' reduction and `psnr` run the fused, deterministic reduction kernel (nrf_mse_pair: one
+launch, optional boolean pixel mask); any other reduction returns the per-element squared error as plain tensors.
+`ssim` wraps kornia in the reference and is not part of the ray-rendering path."""
 import torch
 
 from .losses import mse_pair
 
+_DB_PER_DECADE = -10.0
+
+
+def _squared_error(pred, target, mask):
+    err = (pred - target) ** 2
+    return err if mask is None else err[mask]
+
 
 def mse(image_pred, image_gt, valid_mask=None, reduction='mean'):
-    if reduction != 'mean':
-        value = (image_pred - image_gt) ** 2
-        return value[valid_mask] if valid_mask is not None else value
-    return mse_pair(image_pred, None, image_gt, valid_mask)
+    if reduction == 'mean':
+        return mse_pair(image_pred, None, image_gt, valid_mask)
+    return _squared_error(image_pred, image_gt, valid_mask)
 
 
 def psnr(image_pred, image_gt, valid_mask=None, reduction='mean'):
-    return -10 * torch.log10(mse(image_pred, image_gt, valid_mask, reduction))
+    """Peak signal-to-noise ratio in dB for images in [0, 1]."""
+    return _DB_PER_DECADE * torch.log10(mse(image_pred, image_gt, valid_mask, reduction))
 
 
 def ssim(image_pred, image_gt, reduction='mean'):
