@@ -11,17 +11,27 @@ LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libnerf_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 EXTRA = os.environ.get("NVCC_EXTRA", "").split()
+# NRF_DEBUG_BUILD=1 adds csrc/debug/*.cu (streaming / MMA-rate / store-rate microbenchmarks, the experimental CTA-pair
+# forward, the forward kernels' cycle counters) and their entry points (include/nerf_b200_debug.h).  The product
+# library has none of them and honours no debug environment variable.
+DEBUG = os.environ.get("NRF_DEBUG_BUILD", "") not in ("", "0")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"] + EXTRA
+         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", CSRC] + (["-DNRF_FWD_DEBUG=1"] if DEBUG else []) + EXTRA
 
 
 def _sources():
-    return sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+    src = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+    if DEBUG:
+        src += sorted(os.path.join("debug", f) for f in os.listdir(os.path.join(CSRC, "debug")) if f.endswith(".cu"))
+    return src
 
 
 def _digest():
     h = hashlib.sha256()
-    for f in sorted(os.listdir(CSRC)) + ["../../include/nerf_b200.h"]:
+    files = [f for f in sorted(os.listdir(CSRC)) if os.path.isfile(os.path.join(CSRC, f))]
+    if DEBUG:
+        files += [os.path.join("debug", f) for f in sorted(os.listdir(os.path.join(CSRC, "debug")))]
+    for f in files + ["../../include/nerf_b200.h"]:
         with open(os.path.join(CSRC, f), "rb") as fh:
             h.update(f.encode() + fh.read())
     h.update(" ".join(FLAGS).encode())
@@ -38,7 +48,7 @@ def build(force=False, verbose=False):
     objs = []
 
     def cc(src):
-        obj = os.path.join(LIBDIR, src[:-3] + ".o")
+        obj = os.path.join(LIBDIR, os.path.basename(src)[:-3] + ".o")
         cmd = [NVCC, *FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")

@@ -72,11 +72,15 @@ SIGNATURES = {
     "nrf_light_gather": (I, [P, P, L, I, I, P, P, P]),
     "nrf_light_scatter": (I, [P, P, L, L, P, P]),
     "nrf_w_mapping": (I, [P, P, P, L, F, P, P]),
+    "nrf_shadow_bwd": (I, [P, P, P, P, P, P, P, P, P, L, I, I, I, F, F, F, F, I, P, P, P, P, Z, P]),
+}
+
+# include/nerf_b200_debug.h: present only in a library built with NRF_DEBUG_BUILD=1 (tools/ microbenchmarks)
+DEBUG_SIGNATURES = {
     "nrf_dbg_set_counters": (None, [P]),
     "nrf_dbg_mma_rate": (I, [I, I, P, P]),
     "nrf_dbg_store_rate": (I, [P, ctypes.c_uint64, c_uint32, I, I, I, P, P]),
     "nrf_dbg_stream": (I, [P, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, c_uint32, I, I, I, I, I, I, P]),
-    "nrf_shadow_bwd": (I, [P, P, P, P, P, P, P, P, P, L, I, I, I, F, F, F, F, I, P, P, P, P, Z, P]),
 }
 
 _lib = None
@@ -96,6 +100,11 @@ def load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    for name, (res, args) in DEBUG_SIGNATURES.items():
+        fn = getattr(lib, name, None)
+        if fn is not None:
+            fn.restype = res
+            fn.argtypes = args
     _lib = lib
     return lib
 
@@ -107,4 +116,8 @@ def check(rc, what=""):
 
 
 def call(name, *args):
-    check(getattr(load(), name)(*args), name)
+    fn = getattr(load(), name, None)
+    if fn is None:
+        raise RuntimeError(f"{name} is not exported by {LIB_PATH}"
+                           + (": debug entry points need a library built with NRF_DEBUG_BUILD=1" if name in DEBUG_SIGNATURES else ""))
+    check(fn(*args), name)

@@ -44,6 +44,19 @@ struct ProfScope {
   ~ProfScope() { if (g_prof_on) prof_record(id, st, false, 0); }
 };
 
+// Opt-in to > 48 KB of dynamic shared memory.  The attribute is per DEVICE: `done` is a per-kernel bit mask indexed by
+// the device ordinal, so a process that launches on a second GPU configures the kernel there too.
+#define NRF_OPT_IN_SMEM(kernel, bytes)                                                              \
+  do {                                                                                              \
+    static unsigned long long done__ = 0;                                                           \
+    int dev__ = 0;                                                                                  \
+    NRF_CUDA(cudaGetDevice(&dev__));                                                                \
+    if (dev__ >= 64 || !((done__ >> dev__) & 1ull)) {                                               \
+      NRF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (bytes))); \
+      if (dev__ < 64) done__ |= 1ull << dev__;                                                      \
+    }                                                                                               \
+  } while (0)
+
 static inline cudaStream_t as_stream(nrf_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
 constexpr int kNumSMs = 148;  // B200

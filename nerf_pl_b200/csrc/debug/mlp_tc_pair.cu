@@ -239,7 +239,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTrain ? kThreadsTra
 
 template <bool kFull, bool kTrain>
 static int launch_pair_t(const FwdArgs& a, cudaStream_t st) {
-  static bool configured = false;
+  static bool configured = false;   // debug build, single device
   const int smem_bytes = (int)pair::kSmTotal;
   if (!configured) {
     NRF_CUDA(cudaFuncSetAttribute(pair::mlp_fwd_pair_kernel<kFull, kTrain>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));

@@ -462,12 +462,8 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
 
 template <bool kFull, bool kTrain>
 static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
-  static bool configured = false;
   const int smem_bytes = (int)kSmTotal;
-  if (!configured) {
-    NRF_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<kFull, kTrain>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    configured = true;
-  }
+  NRF_OPT_IN_SMEM((mlp_fwd_kernel<kFull, kTrain>), smem_bytes);
   int dev = 0, sms = kNumSMs;
   NRF_CUDA(cudaGetDevice(&dev));
   NRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -484,15 +480,17 @@ static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
 using namespace nrf;
 using namespace nrf::tc;
 
+#if NRF_FWD_DEBUG
+// Debug build only (NRF_DEBUG_BUILD=1, include/nerf_b200_debug.h); the product library reads no environment variable.
 static unsigned long long* g_dbg_counters = nullptr;
-// Diagnostics: device buffer of >= 8 * gridDim 64-bit counters filled by the next forward launches (null = off).
+// device buffer of >= 8 * gridDim 64-bit counters filled by the next forward launches (null = off)
 extern "C" void nrf_dbg_set_counters(void* dev_ptr) { g_dbg_counters = static_cast<unsigned long long*>(dev_ptr); }
-
-// NRF_FWD_IMPL=pair selects the CTA-pair kernel (mlp_tc_pair.cu); experimental until it is the default
+// NRF_FWD_IMPL=pair selects the experimental CTA-pair kernel (debug/mlp_tc_pair.cu)
 static bool use_pair_kernel() {
   const char* e = getenv("NRF_FWD_IMPL");   // read per call: tools/pair_check.py switches it at run time
   return e && e[0] == 'p';
 }
+#endif
 
 extern "C" size_t nrf_mlp_tc_stash_bytes(int64_t rows, int sigma_only) {
   if (rows <= 0) return 0;
@@ -514,8 +512,10 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
   a.rays = rays; a.z = z; a.n_rows = rows; a.S = n_samples;
   a.num_tiles = (int)((rows + kTileM - 1) / kTileM);
   a.sigma_out = sigma_out; a.rgb_out = rgb_out;
+#if NRF_FWD_DEBUG
   a.dbg = g_dbg_counters;
-  { const char* e = getenv("NRF_DBG_FLAGS"); a.dbg_flags = (NRF_FWD_DEBUG && e) ? atoi(e) : 0; }
+  { const char* e = getenv("NRF_DBG_FLAGS"); a.dbg_flags = e ? atoi(e) : 0; }
+#endif
   cudaStream_t st = as_stream(stream);
   if (stash != nullptr) {
     const size_t need = nrf_mlp_tc_stash_bytes(rows, sigma_only);
@@ -525,10 +525,14 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
     }
     a.stash = static_cast<uint8_t*>(stash);
     a.masks = reinterpret_cast<uint32_t*>(a.stash + (size_t)a.num_tiles * stash_tile_bytes(!sigma_only));
+#if NRF_FWD_DEBUG
     if (use_pair_kernel()) return launch_fwd_pair(!sigma_only, true, a, st);
+#endif
     return sigma_only ? launch_fwd<false, true>(a, st) : launch_fwd<true, true>(a, st);
   }
+#if NRF_FWD_DEBUG
   if (use_pair_kernel()) return launch_fwd_pair(!sigma_only, false, a, st);
+#endif
   return sigma_only ? launch_fwd<false, false>(a, st) : launch_fwd<true, false>(a, st);
 }
 

@@ -359,12 +359,8 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
 
 template <bool kFull>
 static int launch_dgrad_t(const DgradArgs& a, cudaStream_t st) {
-  static bool configured = false;
   const int smem_bytes = (int)kDgSmTotal;
-  if (!configured) {
-    NRF_CUDA(cudaFuncSetAttribute(mlp_dgrad_kernel<kFull>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    configured = true;
-  }
+  NRF_OPT_IN_SMEM(mlp_dgrad_kernel<kFull>, smem_bytes);
   int dev = 0, sms = kNumSMs;
   NRF_CUDA(cudaGetDevice(&dev));
   NRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

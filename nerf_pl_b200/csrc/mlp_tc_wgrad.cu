@@ -470,7 +470,9 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
                         const float* d_sigma, const float* dpre, int64_t n_rows, int num_tiles, int* unit_counter,
                         cudaStream_t st) {
   WgradArgs a{};
+#if NRF_FWD_DEBUG   // debug build only: results are WRONG under these flags (tools/wgrad_probe.py)
   { const char* e = getenv("NRF_DBG_FLAGS"); a.dbg_flags = e ? atoi(e) : 0; }
+#endif
   a.num_tiles = num_tiles; a.n_rows = n_rows;
   a.xstash = xstash;
   a.gstash = gstash;
@@ -522,12 +524,8 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
     a.jobs[i].first_cta = (int)(grid * cum / total_cost);
     cum += stage_cost(a.jobs[i]);
   }
-  static bool configured = false;
   const int smem_bytes = (int)kWgSmTotal + 1024;
-  if (!configured) {
-    NRF_CUDA(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    configured = true;
-  }
+  NRF_OPT_IN_SMEM(mlp_wgrad_kernel, smem_bytes);
   NRF_CUDA(cudaMemsetAsync(unit_counter, 0, kWgMaxJobs * sizeof(int), st));
   ProfScope prof(full ? NRF_K_WGRAD_FULL : NRF_K_WGRAD_SIGMA, st, n_rows);
   mlp_wgrad_kernel<<<grid, kWgThreads, smem_bytes, st>>>(a);

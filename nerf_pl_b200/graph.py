@@ -56,6 +56,11 @@ class GraphedStep:
                 dst.copy_(src, non_blocking=True)
         self.graph.replay()
         self.replays += 1
+        # the captured optimizer step changed the parameters on the device without any host code running: bump their
+        # version counters so that caches keyed on them (NeRF.packed_weights) re-pack on the next EAGER render
+        for o in self.optimizers:
+            for group in o.param_groups:
+                torch.autograd.graph.increment_version(group["params"])
         return self.static_out
 
     def submit(self, *inputs, depth=2):

@@ -10,8 +10,6 @@ import torch
 from . import _lib, ops
 from .ops import _dev, _p, _stream
 
-TC_BACKWARD = True    # False: parameter gradients of the bf16 forward via the fp32 kernels (debug aid)
-
 
 def pack_weights(spec, params, out=None):
     """bf16 UMMA operand images of the parameters (nrf_mlp_tc_pack).  Callers that own the parameters
@@ -44,11 +42,11 @@ def forward_rays(spec, params, rays, z, sigma_only, need_grad, precision, xyz_fr
     if _use_tc(spec, precision):
         if packed is None:
             packed = pack_weights(spec, params)
-        nb = lib.nrf_mlp_tc_stash_bytes(N * S, int(sigma_only)) if (need_grad and TC_BACKWARD) else 0
+        nb = lib.nrf_mlp_tc_stash_bytes(N * S, int(sigma_only)) if need_grad else 0
         stash = torch.empty(nb, dtype=torch.uint8, device=dev) if nb else None
         _lib.call("nrf_mlp_tc_fwd", _p(packed), _p(rays), _p(z), N, S, int(sigma_only), _p(sigma), _p(rgb),
                   _p(stash), nb, _stream())
-        return sigma, rgb, (("tc", packed, stash) if (TC_BACKWARD or not need_grad) else ("tc_recompute",))
+        return sigma, rgb, ("tc", packed, stash)
     ps = spec.params_struct(params)
     nb = lib.nrf_mlp_fp32_workspace_bytes(byref(ps), N * S, N, int(sigma_only), int(need_grad))
     ws = torch.empty(nb, dtype=torch.uint8, device=dev)
@@ -71,19 +69,7 @@ def backward_rays(spec, params, rays, z, sigma_only, saved, d_sigma, d_rgb, rgb,
     if N == 0:
         return ret
     gs = spec.grads_struct(grads)
-    if saved[0] == "tc_recompute":
-        # interim: parameter gradients of the bf16 forward are evaluated by the fp32 kernels at the same
-        # weights (forward re-run with activations kept); replaced by the tcgen05 dgrad/wgrad kernels
-        ps = spec.params_struct(params)
-        nb = lib.nrf_mlp_fp32_workspace_bytes(byref(ps), N * S, N, int(sigma_only), 1)
-        ws = torch.empty(nb, dtype=torch.uint8, device=z.device)
-        sig2 = torch.empty(N, S, device=z.device)
-        rgb2 = None if sigma_only else torch.empty(N, S, 3, device=z.device)
-        _lib.call("nrf_mlp_fp32_fwd_rays", byref(ps), _p(rays), _p(z), N, S, 10, 4, int(sigma_only), 1, _p(sig2),
-                  _p(rgb2), _p(ws), nb, _stream())
-        _lib.call("nrf_mlp_fp32_bwd", byref(ps), byref(gs), None, N * S, N, S, int(sigma_only), _p(d_sigma),
-                  _p(d_rgb), _p(rgb2), _p(ws), nb, _stream())
-    elif saved[0] == "tc":
+    if saved[0] == "tc":
         _, packed, stash = saved
         nb = lib.nrf_mlp_tc_bwd_workspace_bytes(N * S, int(sigma_only))
         ws = torch.empty(nb, dtype=torch.uint8, device=z.device)
@@ -114,12 +100,14 @@ class RenderPass(torch.autograd.Function):
 
     forward(rays, z, noise_or_None, cfg, *params) ->
         (rgb (N,3) [empty when cfg.sigma_only], depth, opacity, disp, weights)
-    cfg: namespace with spec, sigma_only, white_back, noise_std, precision, xyz_freqs, dir_freqs."""
+    cfg: namespace with spec, sigma_only, white_back, noise_std, precision, xyz_freqs, dir_freqs, need_grad."""
 
     @staticmethod
     def forward(ctx, rays, z, noise, cfg, *params):
         ctx.set_materialize_grads(False)      # unused outputs (depth, opacity, disp) arrive as None, not as zero fills
-        need_grad = any(ctx.needs_input_grad[4:])
+        # grad mode is always off inside Function.forward and needs_input_grad ignores torch.no_grad(): the caller
+        # decided (cfg.need_grad) whether this pass will be differentiated, i.e. whether the training stash is written
+        need_grad = bool(cfg.need_grad) and any(ctx.needs_input_grad[4:])
         sigma, rgb_s, saved = forward_rays(cfg.spec, params, rays, z, cfg.sigma_only, need_grad, cfg.precision,
                                            cfg.xyz_freqs, cfg.dir_freqs, getattr(cfg, "packed", None))
         c = ops.composite(sigma, rgb_s, z, rays, noise, cfg.noise_std, cfg.white_back)

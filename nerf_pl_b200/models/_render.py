@@ -6,9 +6,10 @@ sample_pdf kernel -> per-ray sort kernel -> fused MLP -> compositing.  The refer
 chunk loops (train.py:53, rendering.py:151) exist to bound activation memory of the unfused
 PyTorch graph; here no (N*S, 90) tensor is ever materialised, so `chunk` is accepted and ignored.
 
-Random numbers are drawn with torch's CUDA generator in exactly the reference's order
-(rendering.py:231, :178, :36, :41, :178) so a seeded run consumes the same stream; tests
-inject them through the private `_inject` dict instead."""
+Random numbers come from torch's CUDA generator with the reference's DISTRIBUTIONS but not its stream order:
+one fused uniform draw and one fused normal draw per call, sliced per use (the reference makes five separate
+draws: rendering.py:231, :178, :36, :41, :178), so a seeded run sees different jitter / noise values than the
+reference.  Bit-parity checks inject the random tensors through the private `_inject` dict."""
 from types import SimpleNamespace
 
 import torch
@@ -43,7 +44,8 @@ def _model_cfg(model, embeddings, sigma_only, white_back, noise_std):
     return SimpleNamespace(spec=spec, sigma_only=bool(sigma_only), white_back=bool(white_back),
                            noise_std=float(noise_std), precision=precision, packed=packed,
                            xyz_freqs=int(ex.N_freqs), dir_freqs=int(ed.N_freqs),
-                           grad_sinks=model.__dict__.get("_nrf_grad_sinks"))
+                           grad_sinks=model.__dict__.get("_nrf_grad_sinks"),
+                           need_grad=torch.is_grad_enabled() and any(p.requires_grad for p in model.parameters()))
 
 
 def sample_pdf(rays, weights, N_importance, det=False, eps=1e-5, _u=None, _jitter=None):
