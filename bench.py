@@ -24,6 +24,8 @@ NC, NF = 64, 64
 FLOP_PER_SAMPLE_FWDBWD = 3489024
 FLOP_PER_SAMPLE_FWD = 1186816
 FLOP_PER_RAY_TRAIN = FLOP_PER_SAMPLE_FWDBWD * (NC + NC + NF)
+FLOP_SIGMA_FWD = 982528                               # sigma-only model (layers 0..7 + sigma head)
+FLOP_SIGMA_FWDBWD = 982528 + 7 * 131072 + 982528      # + dgrad (7 layers) + wgrad
 
 # The tensor-core MLP kernels of one training step (ids = NRF_K_* of include/nerf_b200.h), with their ALGORITHMIC
 # work per sample row: FLOPs of the GEMM chain, and HBM bytes that have to move once (operand-image
@@ -43,11 +45,13 @@ KERNELS = {
 
 def ncu_traffic():
     """DRAM bytes per launch of each kernel from the committed `ncu --set full` capture (profiles/), or {}."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")) as f:
-            return {int(k): v for k, v in json.load(f)["dram_bytes_per_launch"].items()}
-    except Exception:
-        return {}
+    for name in ("r02_ncu_traffic.json", "r01_ncu_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                return {int(k): v for k, v in json.load(f)["dram_bytes_per_launch"].items()}
+        except Exception:
+            continue
+    return {}
 
 
 WORKLOAD = ("nerf_pl training step: render_rays fwd+bwd + grad all-reduce, 4096 rays/GPU, N_samples=64 N_importance=64, "
@@ -160,7 +164,7 @@ class ClockSampler:
                 "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
-def cpu_reference_rate(n_rays, reps, threads=None, device="cpu"):
+def cpu_reference_rate(n_rays, reps, threads=None, device="cpu", warmup=1):
     """The reference algorithm (oracle port of models/rendering.py) fwd+bwd on the host cores; with device="cuda" the
     same eager-PyTorch fp32 program on the GPU (SURVEY §8d's "before" number: what the reference's own torch path does
     on this B200, reported inside cpu_baseline, never the thing shipped)."""
@@ -178,7 +182,7 @@ def cpu_reference_rate(n_rays, reps, threads=None, device="cpu"):
     noise = {k: v.to(device) for k, v in O.make_noise(n_rays, NC, NF, seed=2).items()}
     opt = torch.optim.Adam([v for p in params for v in p.values()], lr=5e-4, eps=1e-8)   # utils/__init__.py:17-19
     times = []
-    for i in range(reps + 1):
+    for i in range(reps + warmup):
         t0 = time.perf_counter()
         opt.zero_grad()
         out = O.render_rays(params, rays, n_samples=NC, perturb=1.0, noise_std=1.0, n_importance=NF, white_back=True,
@@ -189,7 +193,7 @@ def cpu_reference_rate(n_rays, reps, threads=None, device="cpu"):
         if on_gpu:
             loss.item()
             torch.cuda.synchronize()
-        if i > 0:      # first call is warm-up
+        if i >= warmup:
             times.append(time.perf_counter() - t0)
     times.sort()
     med = times[len(times) // 2]
@@ -213,22 +217,147 @@ def cpu_frame_call_seconds(n_rays):
     return sorted(ts[1:])[1]
 
 
+REFERENCE_SAMPLE_RAYS = 1024     # bounded sample of the 4096-ray batch per CPU step (~0.7 s on 16 cores)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    n = 1024
-    reps = max(1, args.steps)
-    rate, cores, med = cpu_reference_rate(n, reps)
+    n = REFERENCE_SAMPLE_RAYS
+    reps, warm = max(1, args.steps), max(3, args.warmup)       # the same warm-up rule as the GPU arm
+    rate, cores, med = cpu_reference_rate(n, reps, warmup=warm)
     line = {"impl": "reference", "metric": "train_rays_per_sec", "value": rate, "unit": "rays/s", "n_gpus": args.gpus,
-            "steps": reps, "warmup": 1, "ms_per_step": med * 1e3, "higher_is_better": True, "scaling": "weak",
+            "steps": reps, "warmup": warm, "ms_per_step": med * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "rays_per_gpu": RAYS_PER_GPU,
-                       "sample": f"each step = {n} rays of the 4096-ray batch on the host cores (fp32, all threads)"},
+            "config": {"workload": WORKLOAD, "rays_per_gpu": RAYS_PER_GPU, "sample_rays": n,
+                       "sample": f"each step = {n} rays of the 4096-ray batch on the host cores (fp32, all threads); rays/s is "
+                                 f"size-independent for this per-ray workload",
+                       "reference_scope": "one host process on rank 0's host cores" + (
+                           f"; the GPU arm at --gpus {world} is {world} GPUs against this ONE process" if world > 1 else "")},
             "cpu_baseline": {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
-                             "sample": f"{n} rays per step (bounded sample of the 4096-ray batch), median of {reps}"},
+                             "sample": f"{n} rays per step (bounded sample of the 4096-ray batch), median of {reps} after {warm} warm-up steps"},
             "e2e": {"value": rate, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
+
+
+def other_config_rows(torch, dist, dev, rank, world, models, emb, bucket, mse_loss, peaks, timed):
+    """BASELINE.json configs 3, 4 and 5 on this job's GPUs, CUDA-event timed (3 warm-ups, mean of the repetitions, max over
+    ranks), each with its algorithmic FLOP model and the fraction of the BURST bf16 peak (short timed regions).
+      config 3  800x800 test-time frame, chunks of 32768 rays (eval.py:58-86); at N > 1 rays shard over the ranks and the
+                frame is gathered on rank 0 (dist.render_sharded), the gather inside the timed region
+      config 4  LLFF 504x378, 8192 rays per GPU, 64+128 samples, fwd+bwd: (a) NDC rays, (b) use_disp with spheric bounds
+                (datasets/llff.py:236-245)
+      config 5  shadow-mapping step at 128x128 (train_efficient_sm.py:139-208): 4096 camera rays per GPU (depth-only,
+                64+64) + the 16 384-ray light-view depth render (every rank renders it: replicas) + efficient_sm + MSE +
+                backward; (a) light coarse-only without gradients, (b) Light_N_importance = 64 with grad_on_light"""
+    import math
+    from nerf_pl_b200 import dist as nd
+    from nerf_pl_b200.datasets.ray_utils import gen_rays
+    from nerf_pl_b200.models import rendering, rendering_shadows
+    from nerf_pl_b200.models.camera import Camera
+    burst = peaks["bf16_burst"] * 1e12
+    rows = {}
+
+    def max_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    def pose(theta, phi, radius=4.0):
+        th, ph = math.radians(theta), math.radians(phi)
+        t_r = torch.tensor([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, radius], [0, 0, 0, 1.0]])
+        r_ph = torch.tensor([[1, 0, 0, 0], [0, math.cos(ph), -math.sin(ph), 0], [0, math.sin(ph), math.cos(ph), 0], [0, 0, 0, 1.0]])
+        r_th = torch.tensor([[math.cos(th), 0, -math.sin(th), 0], [0, 1, 0, 0], [math.sin(th), 0, math.cos(th), 0], [0, 0, 0, 1.0]])
+        flip = torch.tensor([[-1, 0, 0, 0], [0, 0, 1, 0], [0, 1, 0, 0], [0, 0, 0, 1.0]])
+        return (flip @ r_th @ r_ph @ t_r)[:3, :4].contiguous()
+
+    # ---- config 3 ---------------------------------------------------------------------------------------------------
+    focal800 = 0.5 * 800 / math.tan(0.5 * 0.6911112070083618)
+    frame = gen_rays(pose(30.0, -30.0), 800, 800, focal800, 2.0, 6.0, device=dev)
+
+    def render_slice(r):
+        outs = [rendering.render_rays(models, emb, r[i:i + 32768], NC, False, 0, 0, NF, 1024 * 32, True, True)
+                for i in range(0, r.shape[0], 32768)]
+        return {k: torch.cat([o[k] for o in outs], 0) for k in ("rgb_fine", "depth_fine", "opacity_fine")}
+
+    def render_frame():
+        with torch.no_grad():
+            return nd.render_sharded(render_slice, frame) if world > 1 else render_slice(frame)
+    t = max_ranks(timed(render_frame, reps=3))
+    flop = 640000 * (NC * FLOP_SIGMA_FWD + (NC + NF) * FLOP_PER_SAMPLE_FWD)
+    rows["config3_frame_800x800"] = {
+        "ms": t, "rays_per_s": 640000 / (t * 1e-3), "tflops": flop / (t * 1e-3) / 1e12, "n_gpus": world,
+        "tensor_frac_burst": flop / (t * 1e-3) / (burst * world),
+        "what": "config 3: coarse sigma-only + fine full MLP, 64+64 samples, 20 chunks of 32768 rays under torch.no_grad "
+                "(stash-less inference kernels)" + (f"; rays sharded over {world} ranks, frame gathered on rank 0 inside the "
+                                                    f"timed region" if world > 1 else "")}
+
+    # ---- config 4 ---------------------------------------------------------------------------------------------------
+    H, W, f4 = 378, 504, 407.6
+    c2w4 = torch.tensor([[0.995, -0.03, 0.09, 0.12], [0.02, 0.99, 0.1, -0.08], [-0.1, -0.1, 0.99, 0.05]])
+    pix4 = torch.randperm(H * W, generator=torch.Generator().manual_seed(4 + rank))[:8192].to(dev)
+    tgt4 = torch.rand(8192, 3, device=dev)
+
+    def train_fn(mod, rays, tgt, nf, use_disp):
+        def f():
+            bucket.zero()
+            out = mod.render_rays(models, emb, rays, NC, use_disp, 1.0, 1.0, nf, 1024 * 32, True)
+            mse_loss(out, tgt).backward()
+            bucket.allreduce_mean()
+        return f
+    flop4 = 8192 * FLOP_PER_SAMPLE_FWDBWD * (NC + NC + 128)
+    for tag, rays4, use_disp, what in (
+            ("config4a_llff_ndc", gen_rays(c2w4, H, W, f4, 1.0, 1.0, pix=pix4, ndc=True), False, "NDC rays (near 0, far 1)"),
+            ("config4b_llff_use_disp", gen_rays(c2w4, H, W, f4, 1.33, 10.6, pix=pix4), True, "use_disp, spheric bounds 1.33..10.6")):
+        t = max_ranks(timed(train_fn(rendering, rays4, tgt4, 128, use_disp), reps=10))
+        rows[tag] = {"ms": t, "rays_per_s": world * 8192 / (t * 1e-3), "tflops": world * flop4 / (t * 1e-3) / 1e12,
+                     "tensor_frac_burst": flop4 / (t * 1e-3) / burst, "n_gpus": world,
+                     "what": f"config 4: LLFF 504x378, {what}, 8192 rays per GPU, 64+128 samples, render_rays fwd + MSE + bwd"
+                             f" + gradient all-reduce (no optimizer step)"}
+
+    # ---- config 5 ---------------------------------------------------------------------------------------------------
+    res = (128, 128)
+    cam, light = Camera(30, res), Camera(30, res)
+    cam.set_pose_using_blender_matrix(pose(30.0 + 10.0 * rank, -30.0))
+    light.set_pose_using_blender_matrix(pose(75.0, -50.0))
+
+    def cam_rays(c, pix_ij):          # datasets/blender_efficient_sm.py:98-110
+        M = torch.as_tensor(c.camera, dtype=torch.float32)
+        p = torch.cat([pix_ij + 0.5, torch.ones_like(pix_ij[:, :1])], 1)
+        d = torch.nn.functional.normalize(p @ M.T, dim=-1)
+        o = torch.as_tensor(c.eye_pos, dtype=torch.float32).expand_as(d)
+        return torch.cat([o, d, torch.full_like(d[:, :1], 1.0), torch.full_like(d[:, :1], 200.0)], 1).contiguous()
+
+    ij = torch.stack(torch.meshgrid(torch.arange(128.0), torch.arange(128.0), indexing="xy"), -1).reshape(-1, 2)
+    cam_pix = torch.cat([ij[:4096] + 0.5, torch.ones(4096, 1)], 1).to(dev)
+    light_pix = torch.cat([ij + 0.5, torch.ones(16384, 1)], 1).to(dev)
+    rays_c, rays_l = cam_rays(cam, ij[:4096]).to(dev), cam_rays(light, ij).to(dev)
+    ppc = {"eye_pos": torch.as_tensor(cam.eye_pos, dtype=torch.float32).expand(4096, 3).contiguous().to(dev),
+           "camera": torch.as_tensor(cam.camera, dtype=torch.float32).expand(4096, 3, 3).contiguous().to(dev)}
+    tgt5 = torch.rand(4096, 3, device=dev)
+    for tag, lni, grad_light in (("config5a_shadow_light_coarse_nograd", 0, False), ("config5b_shadow_light_64_grad", 64, True)):
+        def f():
+            bucket.zero()
+            cr = rendering_shadows.render_rays(models, emb, rays_c, NC, False, 1.0, 1.0, NF, 1024 * 32, False)
+            with torch.set_grad_enabled(grad_light):
+                lr = rendering_shadows.render_rays(models, emb, rays_l, NC, False, 1.0, 1.0, lni, 1024 * 32, False)
+            out = rendering_shadows.efficient_sm(cam_pix, light_pix, cr, lr, ppc, light, res, True, lni, "shadow_method_2")
+            mse_loss(out, tgt5).backward()
+            bucket.allreduce_mean()
+        t = max_ranks(timed(f, reps=10))
+        light_rows = 16384 * (NC + (NC + lni if lni else 0))
+        flop5 = 4096 * (NC + NC + NF) * FLOP_SIGMA_FWDBWD + light_rows * (FLOP_SIGMA_FWDBWD if grad_light else FLOP_SIGMA_FWD)
+        rows[tag] = {"ms": t, "camera_rays_per_s": world * 4096 / (t * 1e-3), "tflops": world * flop5 / (t * 1e-3) / 1e12,
+                     "tensor_frac_burst": flop5 / (t * 1e-3) / burst, "n_gpus": world,
+                     "what": f"config 5: 4096 camera rays per GPU (depth-only, 64+64) + 16384 light rays (64+{lni}, "
+                             f"grad_on_light={grad_light}; rendered by every rank) + efficient_sm(shadow_method_2) + MSE + "
+                             f"bwd + gradient all-reduce"}
+    bucket.zero()
+    return rows
 
 
 def run_gpu(args):
@@ -258,7 +387,7 @@ def run_gpu(args):
     from nerf_pl_b200.mlp import forward_rays
     from nerf_pl_b200.models.nerf import Embedding, NeRF
     from nerf_pl_b200.models.rendering import render_rays
-    from oracle import nerf_oracle as O     # input generators + the cpu_baseline leg only
+    from nerf_pl_b200 import synthetic as O     # input generators (oracle/ is imported by the cpu_baseline leg only)
 
     lib = _lib.load()
     _lib.check(lib.nrf_check_device(), "nrf_check_device")
@@ -401,10 +530,12 @@ def run_gpu(args):
             k_ms = tot.value / n.value
             tf = rows * flop_row / (k_ms * 1e-3) / 1e12
             gbs = rows * byte_row / (k_ms * 1e-3) / 1e9
-            f_t, f_h = tf / peaks["bf16_tflops"], gbs / peaks["hbm_gbs"]
+            # the K eager steps are a burst (tens of ms at the maximum SM clock): tensor fraction against the BURST peak
+            f_t, f_h = tf / peaks["bf16_burst"], gbs / peaks["hbm_gbs"]
             table.append({"id": kid, "kernel": f"nrf::tc::{name}", "rows_per_launch": rows, "launches_per_step": n.value / K,
                           "ms_per_launch": k_ms, "ms_per_step": tot.value / K, "flop_per_row": flop_row,
                           "hbm_bytes_per_row": byte_row, "tflops": tf, "tensor_frac": f_t,
+                          "tensor_frac_vs_sustained_peak": tf / peaks["bf16_tflops"],
                           "gbs": gbs, "hbm_frac": f_h, "bound": "hbm" if f_h >= f_t else "tensor",
                           "traffic": traffic.get(kid)})
         if table:
@@ -414,10 +545,14 @@ def run_gpu(args):
                     "kernel": f"{dom['kernel']}, {dom['launches_per_step']:.0f} launches per step, "
                               f"{dom['rows_per_launch']:.0f} sample rows per launch on average",
                     "achieved": dom["gbs"] if hbm else dom["tflops"],
-                    "peak": peaks["hbm_gbs"] if hbm else peaks["bf16_tflops"],
+                    "peak": peaks["hbm_gbs"] if hbm else peaks["bf16_burst"],
                     "unit": "GB/s" if hbm else "TFLOP/s",
                     "frac": dom["hbm_frac"] if hbm else dom["tensor_frac"],
-                    "peak_source": f"{peaks['src']} (" + ("copy bandwidth" if hbm else "sustained: kernel timed inside the step") + ")",
+                    "peak_source": f"{peaks['src']} (" + ("copy bandwidth" if hbm else "burst bf16 peak: K-step timed region at the maximum SM clock") + ")",
+                    # the same kernel on the OTHER roofline: its stash bytes are a design choice, not algorithmic I/O
+                    "tensor_frac": dom["tensor_frac"], "tensor_tflops": dom["tflops"], "hbm_frac": dom["hbm_frac"],
+                    "hbm_bytes_note": "bytes/row = the bf16 operand-image stash this design writes and re-reads (X images "
+                                      "5.4 KB/sample, G images 4.9 KB/sample), not algorithmic I/O of the reference",
                     "ms_per_launch": dom["ms_per_launch"], "share_of_step": dom["ms_per_step"] / ms_eager,
                     "traffic": dom["traffic"],
                     "mlp_kernels_share_of_step": sum(r["ms_per_step"] for r in table) / ms_eager,
@@ -499,20 +634,12 @@ def run_gpu(args):
         "note": "algorithmic bytes per SURVEY 8d (fwd 28 B/sample incl. noise, bwd 40 B/sample); inside a training step "
                 "these five kernels together take ~50 us of 3.7 ms"}
 
-    # BASELINE.json's second headline figure: one 800x800 test-time frame (config 3: perturb=0, noise_std=0, white_back,
-    # 20 calls of 32768 rays, test_time=True) rendered by THIS rank alone with the stepped weights (per-GPU figure; the
-    # ray-sharded N-GPU frame is tools/frame_bench.py)
-    if args.precision == "bf16":
-        frame = gen_rays(c2w, 800, 800, 1111.0, 2.0, 6.0, device=dev)
-
-        def render_frame():
-            with torch.no_grad():
-                return [render_rays(models, emb, frame[i:i + 32768], NC, False, 0, 0, NF, 1024 * 32, True, True)["rgb_fine"]
-                        for i in range(0, frame.shape[0], 32768)]
-        t_frame = timed(render_frame, reps=3)
-        side_rows["frame_800x800"] = {"ms": t_frame, "rays_per_s": 640000 / (t_frame * 1e-3),
-                                      "tflops": 640000 * (NC * 982528 + (NC + NF) * 1186816) / (t_frame * 1e-3) / 1e12,
-                                      "what": "config 3 on one GPU: coarse sigma-only + fine full MLP, 64+64 samples"}
+    # ---- the other BASELINE.json configs (3, 4, 5), each with its FLOP model and burst-peak fraction ---------------
+    other = None
+    if args.precision == "bf16" and not args.no_other_configs:
+        other = other_config_rows(torch, dist, dev, rank, world, models, emb, bucket, mse_loss, peaks, timed)
+        if other and "config3_frame_800x800" in other:
+            side_rows["frame_800x800"] = other["config3_frame_800x800"]
 
     if rank == 0:
         rays_per_s = world * B / (ms * 1e-3)
@@ -524,7 +651,15 @@ def run_gpu(args):
                            "l2": "256 MB flush between timed steps; per-step activation traffic >> 126 MB L2",
                            "launch": "whole step replayed as one CUDA graph (nerf_pl_b200.graph.GraphedStep)",
                            "train_step_flop_per_ray": FLOP_PER_RAY_TRAIN,
-                           "step_tensor_roofline_frac": rays_per_s * FLOP_PER_RAY_TRAIN / world / (peaks["bf16_tflops"] * 1e12)},
+                           # like for like: the K-step `value` is a short burst at the maximum SM clock -> burst peak;
+                           # the 250-step block settles at the power cap -> sustained peak (MEASURED_PEAKS.json)
+                           "step_tensor_frac_burst": rays_per_s * FLOP_PER_RAY_TRAIN / world / (peaks["bf16_burst"] * 1e12),
+                           "e2e_tensor_frac_burst": B / (ms_e2e * 1e-3) * FLOP_PER_RAY_TRAIN / (peaks["bf16_burst"] * 1e12),
+                           "sustained_rays_per_s": world * B / (ms_sustained * 1e-3),
+                           "sustained_ms_per_step": ms_sustained, "sustained_steps": SUSTAIN,
+                           "sustained_tensor_frac": B / (ms_sustained * 1e-3) * FLOP_PER_RAY_TRAIN / (peaks["bf16_tflops"] * 1e12),
+                           "peaks": {"bf16_burst_tflops": peaks["bf16_burst"], "bf16_sustained_tflops": peaks["bf16_tflops"],
+                                     "hbm_gbs": peaks["hbm_gbs"], "source": peaks["src"]}},
                 "clocks": clocks, "gpu_launches": launches,
                 "e2e": {"value": world * B / (ms_e2e * 1e-3), "unit": "rays/s", "ms_per_step": ms_e2e,
                         "api": "nerf_pl_b200.graph.GraphedStep(step).submit(rays_host, rgbs_host) -> handle.result(): the whole "
@@ -537,6 +672,8 @@ def run_gpu(args):
                               "steps": SUSTAIN, "clocks": clocks_sustained,
                               "note": "back-to-back graph replays, no L2 flush (a step streams ~16 GB), one event pair"},
                 "roofline": roof, "side_rows": side_rows}
+        if roof is not None and other is not None:
+            roof["configs"] = other          # the driver keeps `roofline`: rows for BASELINE.json configs 3, 4a, 4b, 5
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, med = cpu_reference_rate(1024, 5)
             line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": cores, "kind": "port",
@@ -580,6 +717,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the config 3 / 4 / 5 rows")
     args = ap.parse_args()
     # exactly ONE line on stdout: libraries that print there (NCCL's version banner under NCCL_DEBUG) go to stderr
     global _RESULT_OUT

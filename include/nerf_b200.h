@@ -144,6 +144,11 @@ int nrf_merge_sort(const float* z_coarse, const float* z_fine, int64_t n_rays, i
  * out (max(nrow_a,nrow_v), ncol_v) int64; one of nrow_a/nrow_v may be 1 (broadcast). */
 int nrf_searchsorted(const float* a, const float* v, int64_t* out, int64_t nrow_a, int64_t nrow_v,
                      int64_t ncol_a, int64_t ncol_v, int side_left, nrf_stream_t stream);
+/* The same for every dtype the reference dispatches (AT_DISPATCH_ALL_TYPES, searchsorted_cuda_kernel.cu:134): `dtype` is
+ * one of NRF_DT_*; a and v share it.  Other codes return NRF_ERR_INVALID with the reference's "not implemented for" text. */
+enum { NRF_DT_F32 = 0, NRF_DT_F64 = 1, NRF_DT_I64 = 2, NRF_DT_I32 = 3, NRF_DT_I16 = 4, NRF_DT_I8 = 5, NRF_DT_U8 = 6 };
+int nrf_searchsorted_typed(const void* a, const void* v, int64_t* out, int64_t nrow_a, int64_t nrow_v,
+                           int64_t ncol_a, int64_t ncol_v, int side_left, int dtype, nrf_stream_t stream);
 
 /* a8  NeRF MLP — models/nerf.py:41-124.  Parameters in the checkpoint layout
  * (utils/__init__.py:55-76): weights (out,in) row-major fp32, biases (out). */

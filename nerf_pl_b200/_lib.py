@@ -52,6 +52,7 @@ SIGNATURES = {
     "nrf_sample_pdf": (I, [P, P, L, I, I, P, P, F, P, P, P, P]),
     "nrf_merge_sort": (I, [P, P, L, I, I, P, P]),
     "nrf_searchsorted": (I, [P, P, P, L, L, L, L, I, P]),
+    "nrf_searchsorted_typed": (I, [P, P, P, L, L, L, L, I, I, P]),
     "nrf_mlp_fp32_workspace_bytes": (Z, [PP, L, L, I, I]),
     "nrf_mlp_fp32_fwd_rays": (I, [PP, P, P, L, I, I, I, I, I, P, P, P, Z, P]),
     "nrf_mlp_fp32_fwd_embedded": (I, [PP, P, L, I, I, P, P, P, Z, P]),

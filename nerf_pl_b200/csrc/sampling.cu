@@ -234,19 +234,20 @@ __global__ void merge_sorted_kernel(const float* __restrict__ zc, const float* _
 // ---------------------------------------------------------------------------------------------
 // a12  torchsearchsorted (searchsorted_cuda_kernel.cu:83-107): one thread per query.
 // ---------------------------------------------------------------------------------------------
-__global__ void searchsorted_kernel(const float* __restrict__ a, const float* __restrict__ v,
+template <typename T>
+__global__ void searchsorted_kernel(const T* __restrict__ a, const T* __restrict__ v,
                                     int64_t* __restrict__ out, int64_t nrow_a, int64_t nrow_v,
                                     int64_t ncol_a, int64_t ncol_v, int64_t nrow_out, int side_left) {
   const int64_t total = nrow_out * ncol_v;
   for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
        idx += (int64_t)gridDim.x * blockDim.x) {
     const int64_t row = idx / ncol_v, col = idx - row * ncol_v;
-    const float* ar = a + (nrow_a == 1 ? 0 : row) * ncol_a;
-    const float val = v[(nrow_v == 1 ? 0 : row) * ncol_v + col];
+    const T* ar = a + (nrow_a == 1 ? 0 : row) * ncol_a;
+    const T val = v[(nrow_v == 1 ? 0 : row) * ncol_v + col];
     int64_t lo = 0, hi = ncol_a;
     while (lo < hi) {
       const int64_t mid = (lo + hi) >> 1;
-      const float am = __ldg(ar + mid);
+      const T am = __ldg(ar + mid);
       const bool go_right = side_left ? (am < val) : (am <= val);
       if (go_right) lo = mid + 1; else hi = mid;
     }
@@ -326,17 +327,39 @@ extern "C" int nrf_merge_sort(const float* z_coarse, const float* z_fine, int64_
   return NRF_OK;
 }
 
-extern "C" int nrf_searchsorted(const float* a, const float* v, int64_t* out, int64_t nrow_a, int64_t nrow_v,
-                                int64_t ncol_a, int64_t ncol_v, int side_left, nrf_stream_t stream) {
+template <typename T>
+static int searchsorted_launch(const void* a, const void* v, int64_t* out, int64_t nrow_a, int64_t nrow_v, int64_t ncol_a,
+                               int64_t ncol_v, int side_left, cudaStream_t st) {
+  const int64_t nrow_out = nrow_a > nrow_v ? nrow_a : nrow_v;
+  searchsorted_kernel<T><<<grid_for(nrow_out * ncol_v, 256), 256, 0, st>>>(
+      static_cast<const T*>(a), static_cast<const T*>(v), out, nrow_a, nrow_v, ncol_a, ncol_v, nrow_out, side_left);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+extern "C" int nrf_searchsorted_typed(const void* a, const void* v, int64_t* out, int64_t nrow_a, int64_t nrow_v,
+                                      int64_t ncol_a, int64_t ncol_v, int side_left, int dtype, nrf_stream_t stream) {
   // same contract as torchsearchsorted/src/torchsearchsorted/searchsorted.py:23-31
   NRF_REQUIRE(nrow_a >= 1 && nrow_v >= 1 && ncol_a >= 1 && ncol_v >= 0, "nrf_searchsorted: bad sizes");
   NRF_REQUIRE(nrow_a == nrow_v || nrow_a == 1 || nrow_v == 1,
               "`a` and `v` must have the same number of rows or one of them must have only one");
   if (ncol_v == 0) return NRF_OK;
   NRF_REQUIRE(a && v && out, "nrf_searchsorted: null pointer");
-  const int64_t nrow_out = nrow_a > nrow_v ? nrow_a : nrow_v;
-  searchsorted_kernel<<<grid_for(nrow_out * ncol_v, 256), 256, 0, as_stream(stream)>>>(
-      a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, nrow_out, side_left);
-  NRF_LAUNCH_CHECK();
-  return NRF_OK;
+  cudaStream_t st = as_stream(stream);
+  switch (dtype) {   // AT_DISPATCH_ALL_TYPES (searchsorted_cuda_kernel.cu:134)
+    case NRF_DT_F32: return searchsorted_launch<float>(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, st);
+    case NRF_DT_F64: return searchsorted_launch<double>(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, st);
+    case NRF_DT_I64: return searchsorted_launch<long long>(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, st);
+    case NRF_DT_I32: return searchsorted_launch<int>(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, st);
+    case NRF_DT_I16: return searchsorted_launch<short>(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, st);
+    case NRF_DT_I8: return searchsorted_launch<signed char>(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, st);
+    case NRF_DT_U8: return searchsorted_launch<unsigned char>(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, st);
+  }
+  set_error("nrf_searchsorted: \"searchsorted cuda\" not implemented for dtype code %d", dtype);
+  return NRF_ERR_INVALID;
+}
+
+extern "C" int nrf_searchsorted(const float* a, const float* v, int64_t* out, int64_t nrow_a, int64_t nrow_v,
+                                int64_t ncol_a, int64_t ncol_v, int side_left, nrf_stream_t stream) {
+  return nrf_searchsorted_typed(a, v, out, nrow_a, nrow_v, ncol_a, ncol_v, side_left, NRF_DT_F32, stream);
 }

@@ -160,6 +160,17 @@ def merge_sort(z_coarse, z_fine):
     return out
 
 
+_SEARCHSORTED_DTYPES = {torch.float32: 0, torch.float64: 1, torch.int64: 2, torch.int32: 3, torch.int16: 4, torch.int8: 5,
+                        torch.uint8: 6}
+
+
+def _dev_any(t, name):
+    """Contiguous CUDA tensor of any dtype (no CPU path)."""
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (nerf_pl_b200 has no CPU path)")
+    return t.contiguous()
+
+
 def searchsorted(a, v, out=None, side="left"):
     """Drop-in for torchsearchsorted.searchsorted (src/torchsearchsorted/searchsorted.py:20-53)."""
     assert len(a.shape) == 2, "input `a` must be 2-D."
@@ -175,9 +186,14 @@ def searchsorted(a, v, out=None, side="left"):
         assert out.is_contiguous()
     else:
         out = torch.empty(shape, device=v.device, dtype=torch.long)
-    a, v = _dev(a, "a"), _dev(v, "v")
-    _lib.call("nrf_searchsorted", _p(a), _p(v), _p(out), a.shape[0], v.shape[0], a.shape[1], v.shape[1],
-              1 if side == "left" else 0, _stream())
+    if a.dtype != v.dtype:
+        raise RuntimeError(f"expected `a` and `v` of the same dtype, got {a.dtype} and {v.dtype}")
+    code = _SEARCHSORTED_DTYPES.get(a.dtype)
+    if code is None:      # the reference's dispatch error (AT_DISPATCH_ALL_TYPES, searchsorted_cuda_kernel.cu:134)
+        raise RuntimeError(f'"searchsorted cuda" not implemented for \'{str(a.dtype).replace("torch.", "")}\'')
+    a, v = _dev_any(a, "a"), _dev_any(v, "v")
+    _lib.call("nrf_searchsorted_typed", _p(a), _p(v), _p(out), a.shape[0], v.shape[0], a.shape[1], v.shape[1],
+              1 if side == "left" else 0, code, _stream())
     return out
 
 

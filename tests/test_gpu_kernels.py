@@ -62,6 +62,31 @@ def test_searchsorted_golden_and_reference_contract(dev):
         ops.searchsorted(torch.zeros(3, 4, device=dev), torch.zeros(2, 4, device=dev))
 
 
+@pytest.mark.parametrize("dtype", [torch.float64, torch.int64, torch.int32, torch.int16, torch.int8, torch.uint8])
+def test_searchsorted_all_dtypes_vs_numpy(dev, dtype):
+    """The reference dispatches every torch dtype (AT_DISPATCH_ALL_TYPES, searchsorted_cuda_kernel.cu:134); bit-exact against
+    numpy.searchsorted, ties included (small integer ranges), both sides, broadcast rows; unsupported dtypes raise the
+    reference's dispatch error text."""
+    from nerf_pl_b200 import ops
+    rng = np.random.RandomState(1)
+    for Ba, Bv, A, V in [(1, 40, 50, 12), (40, 1, 7, 30), (33, 33, 200, 5)]:
+        if dtype.is_floating_point:
+            a, v = np.sort(rng.rand(Ba, A), 1), rng.rand(Bv, V)
+        else:
+            hi = 100 if dtype in (torch.int8, torch.uint8) else 1000
+            lo = 0 if dtype == torch.uint8 else -hi
+            a, v = np.sort(rng.randint(lo, hi, (Ba, A)), 1), rng.randint(lo, hi, (Bv, V))
+        ta, tv = torch.from_numpy(a).to(dtype), torch.from_numpy(v).to(dtype)
+        for side in ("left", "right"):
+            got = ops.searchsorted(ta.to(dev), tv.to(dev), side=side)
+            assert got.dtype == torch.long
+            assert np.array_equal(got.cpu().numpy(), O.searchsorted_rows(ta.numpy(), tv.numpy(), side))
+    with pytest.raises(RuntimeError, match="not implemented for"):
+        ops.searchsorted(torch.zeros(1, 4, device=dev, dtype=torch.float16), torch.zeros(1, 4, device=dev, dtype=torch.float16))
+    with pytest.raises(RuntimeError, match="same dtype"):
+        ops.searchsorted(torch.zeros(1, 4, device=dev), torch.zeros(1, 4, device=dev, dtype=torch.float64))
+
+
 def test_searchsorted_random_vs_numpy(dev):
     # the reference's own test loop (test_searchsorted.py:27-44), one repeat per shape
     from nerf_pl_b200 import ops
@@ -74,6 +99,11 @@ def test_searchsorted_random_vs_numpy(dev):
                 for side in ("left", "right"):
                     got = ops.searchsorted(torch.from_numpy(a).to(dev), torch.from_numpy(v).to(dev), side=side)
                     assert np.array_equal(got.cpu().numpy(), O.searchsorted_rows(a, v, side))
+
+
+# Measured on B200 (profiles/r02_parity.json: sample_pdf_vs_reference_golden); the bounds leave 2x headroom.
+SAME_CDF_ROWS_MIN = 0.25
+FLIP_RATE_MAX = 5e-3
 
 
 def test_sample_pdf_golden_and_bit_exact_given_cdf(dev):
@@ -92,12 +122,16 @@ def test_sample_pdf_golden_and_bit_exact_given_cdf(dev):
     same_row = (cdf.cpu() == ref_cdf).all(1)
     # torch's CPU sum() is a SIMD tree whose order no device reduction reproduces, so the normaliser (and
     # with it the cdf) may differ in the last ulp on some rows; rows with an identical cdf must match exactly
-    print(f"rows with bit-identical cdf: {same_row.float().mean().item():.2f}")
-    assert same_row.any()
+    same_frac = same_row.float().mean().item()
+    print(f"rows with bit-identical cdf: {same_frac:.2f}")
+    assert same_frac >= SAME_CDF_ROWS_MIN, f"only {same_frac:.2f} of the rows have a bit-identical cdf"
     assert np.array_equal(z.cpu().numpy()[same_row.numpy()], c["z"][same_row.numpy()])
     np.testing.assert_allclose(cdf.cpu().numpy(), ref_cdf.numpy(), rtol=0, atol=2.5e-7)
     flips = (z.cpu() != torch.from_numpy(c["z"])).float().mean().item()
-    assert flips < 0.01, f"bin flip rate {flips}"
+    import _parity
+    _parity.record("sample_pdf_vs_reference_golden", rows_with_bit_identical_cdf=same_frac, fine_sample_flip_rate=flips,
+                   cdf_max_abs_diff=float((cdf.cpu() - ref_cdf).abs().max()))
+    assert flips < FLIP_RATE_MAX, f"bin flip rate {flips}"
 
 
 @pytest.mark.parametrize("nc,nf", [(64, 64), (64, 128), (16, 24), (5, 0), (1, 1)])

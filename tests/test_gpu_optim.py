@@ -186,6 +186,20 @@ def test_graphed_step_matches_eager(dev):
         ra = render_rays(a, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
         rb = render_rays(b, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
     assert (ra["rgb_fine"] - rb["rgb_fine"]).abs().max().item() < 2e-2
+    # replays change the parameters without running host code; the SECOND eager render between replays must
+    # not reuse operand images packed before those replays (GraphedStep bumps the parameter versions after a replay):
+    # replay, eager render, replay, eager render == a render with freshly packed weights, bit for bit
+    from nerf_pl_b200 import mlp as _mlp
+    for _ in range(2):
+        r2, c2 = batch()
+        graphed(r2, c2)
+        with torch.no_grad():
+            cached = render_rays(a, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
+            for m in a:
+                m.__dict__.pop("_nrf_pack", None)          # force a fresh pack of the current parameters
+            fresh = render_rays(a, emb, r.to(dev), N_samples=32, N_importance=32, perturb=0, noise_std=0, test_time=True)
+        assert torch.equal(cached["rgb_fine"], fresh["rgb_fine"]), "stale bf16 operand images after a graph replay"
+    graphed.close()
 
 
 # ---- a28: sgd / radam / ranger over the flat buffers (tests/make_golden_optim.py: the reference's own classes) ----------

@@ -184,15 +184,23 @@ def test_full_width_bf16_vs_oracle(dev, variant, near, far, test_time):
     margin = 2e-3
     stable = ((aux["raw_coarse"][:, -1].abs() > margin) & (aux["raw_fine"][:, -1].abs() > margin)).detach().numpy()
     print(f"rays away from the last-sample discontinuity: {stable.mean():.3f}")
-    assert stable.mean() > 0.5
+    assert stable.mean() >= 0.95      # random-init weights + unit noise: |raw_last| < 2e-3 for ~0.3 % of the rays
+    import _parity
+    rec = {"stable_fraction": float(stable.mean())}
     for k in sorted(ref):
         r = ref[k].detach().numpy()
         g = got[k].detach().cpu().numpy()
         ok = ~np.isnan(r) & (stable if r.ndim == 1 else stable[:, None])
         err = np.abs(g[ok] - r[ok]).max()
         print(f"{k}: max abs err {err:.3e} (range {np.abs(r[ok]).max():.2f})")
-        tol = 2e-3 * (far if k.startswith("depth") else 1.0) * (20.0 if k.startswith("disp") else 1.0)
+        rec["max_abs_err/" + k] = float(err)
+        if k.startswith("disp"):
+            continue                  # 1 / (depth / opacity): unbounded where opacity -> 0; reported only
+        # north_star: 2e-3 absolute on rgb / opacity; depth (= sum w z, z up to `far` = 6 here) 2e-3 * far, measured
+        # values in profiles/r02_parity.json (the 1..200 bounds are covered by tests/test_gpu_parity_sizes.py)
+        tol = 2e-3 * (far if k.startswith("depth") else 1.0)
         assert err < tol, k
+    _parity.record(f"full_width_bf16_2_6/{variant}/test_time={int(test_time)}", **rec)
     if not test_time and variant == "rgb":
         g = torch.Generator().manual_seed(5)
         loss_r = loss_g = 0
