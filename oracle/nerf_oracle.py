@@ -124,7 +124,7 @@ def composite(sigmas: Tensor, rgbs: Optional[Tensor], z: Tensor, dirs: Tensor,
     alpha = 1 - torch.exp(-delta * torch.relu(raw))
     trans = torch.cumprod(torch.cat([torch.ones_like(alpha[:, :1]), 1 - alpha + 1e-10], -1), -1)[:, :-1]
     w = alpha * trans
-    out = {"weights": w, "opacity": w.sum(1), "depth": (w * z).sum(-1), "raw": raw}
+    out = {"weights": w, "opacity": w.sum(1), "depth": (w * z).sum(-1), "raw": raw, "rgbs": rgbs}
     out["disp"] = 1.0 / torch.max(1e-10 * torch.ones_like(out["depth"]), out["depth"] / w.sum(-1))
     if rgbs is not None:
         rgb = (w.unsqueeze(-1) * rgbs).sum(-2)
@@ -229,6 +229,8 @@ def render_rays(params: Sequence[Dict[str, Tensor]], rays: Tensor, *, n_samples:
             res["disp_map_coarse"] = c["disp"]
     aux["weights_coarse"] = c["weights"]
     aux["raw_coarse"] = c["raw"]
+    if c["rgbs"] is not None:
+        aux["rgbs_coarse"] = c["rgbs"]
     if n_importance > 0:
         if "z_fine" in noise:
             zf = noise["z_fine"]
@@ -247,6 +249,8 @@ def render_rays(params: Sequence[Dict[str, Tensor]], rays: Tensor, *, n_samples:
             res["disp_map_fine"] = f["disp"]
         aux["weights_fine"] = f["weights"]
         aux["raw_fine"] = f["raw"]
+        if f["rgbs"] is not None:
+            aux["rgbs_fine"] = f["rgbs"]
     if return_aux:
         return res, aux
     return res

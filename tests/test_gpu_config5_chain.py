@@ -143,7 +143,7 @@ def _check(dev, name, case, precision, lni, grad_on_light):
     rec = {"loss_ref": case["loss"], "loss_got": loss}
     aux_c, aux_l = case["aux"]
     # (1) the depth maps that feed the shadow test
-    d_tol = 2e-5 * 200.0 if precision == "fp32" else 0.5
+    d_tol = 2e-5 * 200.0 if precision == "fp32" else 3e-2        # bf16 at bounds 1..200: measured 1.6e-2 (tests/_parity.py)
     for side, ref, aux in (("cam", case["cam"], aux_c), ("light", case["light"], aux_l)):
         stable = P.last_sample_stable(aux)
         rec[f"stable_fraction/{side}"] = float(stable.mean())
@@ -156,7 +156,7 @@ def _check(dev, name, case, precision, lni, grad_on_light):
             assert e < d_tol, f"{name} {side} {k}: {e:.3e}"
     # (2) the shadow values: rays that landed in the same light texel agree; the others are counted
     s_tol = 1e-4 if precision == "fp32" else 5e-3
-    flip_bound = 1e-3 if precision == "fp32" else 0.10
+    flip_bound = 1e-3 if precision == "fp32" else 0.01           # measured: fp32 0, bf16 0.2-0.3 % of the camera rays
     for k in ("rgb_coarse", "rgb_fine"):
         e = (out[k].detach().cpu() - case["out"][k]).abs().max(-1)[0].numpy()
         moved = e >= s_tol
@@ -168,7 +168,10 @@ def _check(dev, name, case, precision, lni, grad_on_light):
     assert rec["loss_rel_err"] < (1e-4 if precision == "fp32" else 3e-2)
     # (3) parameter gradients of both models
     ref_grads = case["grads"][grad_on_light]
-    tol = {"fp32": {"tensor": 2e-2, "model": 2e-3}, "bf16": {"tensor": 0.25, "model": 0.1}}[precision]
+    # fp32: measured 2.2e-5 per tensor / 5e-6 per model.  bf16: the rays that changed light texel (above) carry a different
+    # shadow gradient, and shadow_method_2's min-max normalisation couples every ray to the two extremal ones: measured up to
+    # 0.20 per tensor / 6.8e-2 per model against 5e-2 / 2e-2 for plain render_rays
+    tol = {"fp32": {"tensor": 1e-3, "model": 1e-4}, "bf16": {"tensor": 0.35, "model": 0.12}}[precision]
     for mi, m in enumerate(models):
         num = den = 0.0
         worst, worst_name = 0.0, ""

@@ -101,9 +101,11 @@ def test_searchsorted_random_vs_numpy(dev):
                     assert np.array_equal(got.cpu().numpy(), O.searchsorted_rows(a, v, side))
 
 
-# Measured on B200 (profiles/r02_parity.json: sample_pdf_vs_reference_golden); the bounds leave 2x headroom.
+# Measured on B200 (profiles/r02_parity.json: sample_pdf_vs_reference_golden): 0.42 of the rows have a cdf bit-identical to
+# torch's CPU cdf (the rest differ by one ulp of the normaliser: torch's CPU sum is a SIMD tree no device reduction
+# reproduces, and the reference run on a GPU uses yet another order), and none of the 2048 fine samples changes bin.
 SAME_CDF_ROWS_MIN = 0.25
-FLIP_RATE_MAX = 5e-3
+FLIP_RATE_MAX = 1e-3
 
 
 def test_sample_pdf_golden_and_bit_exact_given_cdf(dev):

@@ -22,18 +22,13 @@ import _parity as P
 
 pytestmark = pytest.mark.gpu
 
-# bf16 tensor-core MLP, absolute errors on rays away from the last-sample discontinuity.
-#   rgb / opacity: north_star 2e-3.
-#   depth: north_star 2e-3 holds at the 2..6 bounds it was written for.  depth = sum w_i z_i scales with `far`: at the
-#   fork's 1..200 bounds the same RELATIVE agreement of the weights gives an absolute deviation of a few 1e-2; the
-#   stated bounds are 3x the measured maxima recorded in profiles/r02_parity.json.
-TOL = {
-    "rgb": 2e-3, "opacity": 2e-3,
-    "depth@6": 2e-3 * 6, "depth@200": 0.5, "depth@ndc": 2e-3,
-    "disp_map": None,      # 1 / max(1e-10, depth / opacity): unbounded where opacity -> 0; reported, not asserted
-}
+# Output tolerances: tests/_parity.py BF16_TOL (north_star 2e-3 absolute on rgb / depth / opacity; depth 3e-2 at the fork's
+# 1..200 bounds, measured 1.6e-2) and the fp32-mode 2e-5 relative bound.  Parameter gradients (relative L2 against the fp32
+# oracle): SURVEY 8c(iv) 2e-2 over a model's gradient; per tensor the near-cancelling first-layer gradients reach 1.5e-2 at
+# config 2 and 8.4e-2 at bounds 1..200 with use_disp (measured, profiles/r02_parity.json): stated 5e-2 / 1.5e-1.
 GRAD_TOL_BF16 = {"tensor": 5e-2, "model": 2e-2}      # 2e-2 over a model's gradient; 5e-2 per tensor
-GRAD_TOL_FP32 = {"tensor": 1e-2, "model": 2e-4}
+GRAD_TOL_FP32 = {"tensor": 1e-3, "model": 1e-4}       # measured 8e-5 / 9e-7 at 4096 rays
+GRAD_TOL_BF16_FORK = {"tensor": 1.5e-1, "model": 2e-2}
 
 
 @pytest.fixture(scope="module")
@@ -85,45 +80,6 @@ def _gpu_render(dev, precision, variant, params, rays, noise, aux, kw):
     return models, got
 
 
-def _compare_outputs(tag, ref, got, aux, depth_key, precision):
-    """Asserts TOL on the stable rays, bounds the excluded rays separately, records everything."""
-    stable = P.last_sample_stable(aux)
-    frac = float(stable.mean())
-    rec = {"stable_fraction": frac, "n_rays": float(stable.size)}
-    assert frac >= 0.95, f"{tag}: only {frac:.3f} of the rays are away from the last-sample discontinuity"
-    assert sorted(got) == sorted(ref)
-    for k in sorted(ref):
-        r, g = ref[k].detach().numpy(), got[k].detach().cpu().numpy()
-        ok = stable if r.ndim == 1 else stable[:, None] & np.ones_like(r, dtype=bool)
-        ok = ok & ~np.isnan(r)
-        err = float(np.abs(g[ok] - r[ok]).max())
-        rec[f"max_abs_err/{k}"] = err
-        rec[f"range/{k}"] = float(np.abs(r[ok]).max())
-        kind = k.rsplit("_", 1)[0]
-        if precision == "fp32":
-            tol = 2e-5 * max(1.0, rec[f"range/{k}"])       # fp32 mode: 1e-5-class relative to the key's range
-        else:
-            tol = TOL[depth_key] if kind == "depth" else TOL.get(kind)
-        if kind == "disp_map":
-            tol = None
-        rec[f"tol/{k}"] = -1.0 if tol is None else tol
-        if tol is not None:
-            assert err < tol, f"{tag} {k}: max abs err {err:.3e} >= {tol:.1e}"
-    # excluded rays: their opacity must still be one of the two values the discontinuity allows (last alpha 0 or 1)
-    if (~stable).any() and precision == "bf16":
-        for pas in ("coarse", "fine"):
-            key = f"opacity_{pas}"
-            if key not in ref or f"weights_{pas}" not in aux:
-                continue
-            a, b = P.opacity_candidates(aux[f"weights_{pas}"])
-            g = got[key].detach().cpu()
-            bad = torch.from_numpy(~stable)
-            dev_ = torch.minimum((g - a).abs(), (g - b).abs())[bad]
-            rec[f"excluded_rays_max_dev/{key}"] = float(dev_.max())
-            assert float(dev_.max()) < 5e-3, f"{tag} {key}: an excluded ray is at neither side of the discontinuity"
-    return rec
-
-
 def _mse_backward(models, got, tgt, dev):
     from nerf_pl_b200.losses import loss_dict
     loss_dict["mse"]()(got, tgt.to(dev)).backward()
@@ -141,7 +97,7 @@ def test_config2_4096_rays_fwd_bwd_vs_oracle(dev, precision):
     params, noise, ref, aux, tgt, kw = _oracle_case("c2", rays, 64, 64, "rgb", False, False, True, 2, True)
     try:
         models, got = _gpu_render(dev, precision, "rgb", params, rays, noise, aux, kw)
-        rec = _compare_outputs(f"config2/{precision}", ref, got, aux, "depth@6", precision)
+        rec = P.compare_outputs(f"config2/{precision}", ref, got, aux, rays, True, precision)
         _mse_backward(models, got, tgt, dev)
         tolg = GRAD_TOL_BF16 if precision == "bf16" else GRAD_TOL_FP32
         for mi, (worst, whole, name) in enumerate(P.grad_errors(params, models)):
@@ -170,7 +126,7 @@ def test_config4_8192_rays_fwd_vs_oracle(dev):
     params, noise, ref, aux, tgt, kw = _oracle_case("c4", rays, 64, 128, "rgb", False, False, False, 5, False)
     with torch.no_grad():
         models, got = _gpu_render(dev, "bf16", "rgb", params, rays, noise, aux, kw)
-    rec = _compare_outputs("config4/bf16", ref, got, aux, "depth@ndc", "bf16")
+    rec = P.compare_outputs("config4/bf16", ref, got, aux, rays, False, "bf16")
     P.record("config4_8192x(64+128)_fwd/bf16", **rec)
 
 
@@ -181,7 +137,7 @@ def test_config3_32768_ray_test_chunk_vs_oracle(dev):
     params, noise, ref, aux, tgt, kw = _oracle_case("c3", rays, 64, 64, "rgb", False, True, True, 8, False)
     with torch.no_grad():
         models, got = _gpu_render(dev, "bf16", "rgb", params, rays, noise, aux, kw)
-    rec = _compare_outputs("config3/bf16", ref, got, aux, "depth@6", "bf16")
+    rec = P.compare_outputs("config3/bf16", ref, got, aux, rays, True, "bf16")
     P.record("config3_32768_test_chunk/bf16", **rec)
 
 
@@ -221,7 +177,7 @@ def test_bf16_fork_bounds_1_200_vs_oracle(dev, variant, use_disp, test_time):
     grad_mode = torch.enable_grad() if not test_time else torch.no_grad()
     with grad_mode:
         models, got = _gpu_render(dev, "bf16", variant, params, rays, noise, aux, kw)
-    rec = _compare_outputs(name, ref, got, aux, "depth@200", "bf16")
+    rec = P.compare_outputs(name, ref, got, aux, rays, True, "bf16", far200=True)
     if not test_time:
         # gradient of a smooth probe over the stable rays' bounded outputs (rgb, opacity; depth / far)
         stable = torch.from_numpy(P.last_sample_stable(aux))
@@ -242,8 +198,8 @@ def test_bf16_fork_bounds_1_200_vs_oracle(dev, variant, use_disp, test_time):
             rec[f"grad_rel_l2/model{mi}/worst_tensor"] = worst
             rec[f"grad_rel_l2/model{mi}/whole"] = whole
             rec[f"grad_worst_tensor_name/model{mi}"] = nm
-            assert whole < GRAD_TOL_BF16["model"], f"{name} model {mi}: whole-gradient relative L2 error {whole:.2e}"
-            assert worst < GRAD_TOL_BF16["tensor"], f"{name} model {mi} {nm}: {worst:.2e}"
+            assert whole < GRAD_TOL_BF16_FORK["model"], f"{name} model {mi}: whole-gradient relative L2 error {whole:.2e}"
+            assert worst < GRAD_TOL_BF16_FORK["tensor"], f"{name} model {mi} {nm}: {worst:.2e}"
     P.record(f"bf16_bounds_1_200/{variant}/use_disp={int(use_disp)}/test_time={int(test_time)}", **rec)
 
 
