@@ -27,6 +27,11 @@ int nrf_dbg_mma_rate(int reps, int grid, void* out, nrf_stream_t stream);
 int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint32_t piece, int steps, int depth, int grid, void* out,
                        nrf_stream_t stream);
 
+/* Measurement aid: `warps` (4 / 8 / 16) warps per CTA read the 512 TMEM columns of their lane quarter `reps` times with
+ * tcgen05.ld 32x32b .x16 (mode bit 0: .x32); mode bit 1: one thread issues back-to-back MMAs meanwhile.
+ * out[2 cta] (u64, device) = cycles of the slowest warp, out[2 cta + 1] = MMAs retired meanwhile. */
+int nrf_dbg_tmem_rate(int warps, int reps, int mode, int grid, void* out, nrf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,12 +11,12 @@ LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libnerf_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 EXTRA = os.environ.get("NVCC_EXTRA", "").split()
-# NRF_DEBUG_BUILD=1 adds csrc/debug/*.cu (streaming / MMA-rate / store-rate microbenchmarks, the experimental CTA-pair
+# NRF_DEBUG_BUILD=1 (2: only the light per-warp trace points in the forward kernel) adds csrc/debug/*.cu (streaming / MMA-rate / store-rate microbenchmarks, the experimental CTA-pair
 # forward, the forward kernels' cycle counters) and their entry points (include/nerf_b200_debug.h).  The product
 # library has none of them and honours no debug environment variable.
 DEBUG = os.environ.get("NRF_DEBUG_BUILD", "") not in ("", "0")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", CSRC] + (["-DNRF_FWD_DEBUG=1"] if DEBUG else []) + EXTRA
+         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", CSRC] + ([f"-DNRF_FWD_DEBUG={os.environ['NRF_DEBUG_BUILD']}"] if DEBUG else []) + EXTRA
 
 
 def _sources():

@@ -110,6 +110,95 @@ __global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, unsigned long
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
 }
 
+
+// ---- TMEM read rate ------------------------------------------------------------------------------------
+// `warps` (4, 8 or 16) warps each read their TMEM lane quarter with tcgen05.ld.32x32b.x16 (or .x32), `reps` passes over
+// the 512 columns split among the warps of a quarter; optionally one more thread issues back-to-back MMAs into the same
+// TMEM meanwhile (mode bit 1).  out[cta * 2] = cycles of the slowest reader warp, out[cta * 2 + 1] = MMAs retired.
+__global__ void __launch_bounds__(64 + 16 * 32, 1) tmem_rate_kernel(int warps, int reps, int mode, unsigned long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t s_tmem;
+  __shared__ unsigned long long s_max;
+  __shared__ volatile int s_stop;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); s_max = 0; s_stop = 0; }
+  for (int i = threadIdx.x; i < 2 * 32768 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  fence_async_smem();
+  if (warp == 1) tmem_alloc(&s_tmem, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s_tmem;
+  unsigned long long mmas = 0;
+  if (warp == 1 && lane == 0 && (mode & 2)) {
+    const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
+    const uint64_t a_desc = make_desc_sw128(smem_u32(smem), 16, 1024);
+    const uint64_t b_desc = make_desc_sw128(smem_u32(smem + 32768), 16, 1024);
+    uint32_t ph = 0;
+    while (!s_stop) {
+      for (int r = 0; r < 16; ++r) umma_ss(tmem_base + (r & 1) * 256, a_desc + 2 * (r & 3), b_desc + 2 * (r & 3), idesc, 1);
+      umma_commit(&bar);
+      mbar_wait(&bar, ph);
+      ph ^= 1;
+      mmas += 16;
+    }
+    out[blockIdx.x * 2 + 1] = mmas;
+  } else if (warp >= 2 && warp < 2 + warps) {
+    const int q = warp & 3, sub = (warp - 2) >> 2, per_q = warps / 4;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint32_t acc = 0;
+    const long long t0 = clock64();
+    if (mode & 12) {
+      // shared-memory traffic instead of TMEM reads: mode bit 2 = STS.128 (512 B per warp instruction, conflict free),
+      // bit 3 = LDS.128; 64 KB per pass and CTA, into the upper half of the operand buffers (the MMAs read garbage)
+      uint32_t* base = reinterpret_cast<uint32_t*>(smem + 32768 + 16384) + (warp - 2) * 128 + lane * 4;   // 16 KB window
+      for (int r = 0; r < reps; ++r) {
+        for (int i = 0; i < 128 / warps * 1; ++i) {     // warps * (128 / warps) * 512 B = 64 KB per pass
+          uint32_t* p = base + (i & 1) * (warps * 128);
+          if (mode & 4) {
+            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(smem_u32(p)), "r"(acc) : "memory");
+          } else {
+            uint32_t a0, a1, a2, a3;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3) : "r"(smem_u32(p)) : "memory");
+            acc ^= a0 ^ a1 ^ a2 ^ a3;
+          }
+        }
+      }
+    } else
+    for (int r = 0; r < reps; ++r) {
+      if (mode & 1) {
+        for (int c = sub * 32; c < 512; c += per_q * 32) {
+          uint32_t v[32];
+          tmem_ld32(t_lane + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc ^= v[j];
+        }
+      } else {
+        for (int c = sub * 16; c < 512; c += per_q * 16) {
+          uint32_t v[16];
+          tmem_ld16(t_lane + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) acc ^= v[j];
+        }
+      }
+    }
+    const unsigned long long dt = (unsigned long long)(clock64() - t0);
+    if (acc == 0x12345678u) out[blockIdx.x * 2 + 1] = acc;
+    atomicMax(&s_max, dt);
+  }
+  // readers done -> stop the MMA thread
+  if (warp >= 2 && warp < 2 + warps) {
+    named_bar_sync(3, warps * 32);      // reader warps only
+    if (threadIdx.x == 64) { s_stop = 1; out[blockIdx.x * 2] = s_max; }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
+}
+
 }  // namespace tc
 }  // namespace nrf
 
@@ -148,6 +237,16 @@ extern "C" int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint
   NRF_CUDA(cudaFuncSetAttribute(store_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
   store_rate_kernel<<<grid, 32, 65536, as_stream(stream)>>>(static_cast<uint8_t*>(dst), cta_stride, piece, steps, depth,
                                                            static_cast<unsigned long long*>(out));
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+// TMEM read-rate microbenchmark: see tmem_rate_kernel.  mode bit 0: .x32 loads (else .x16); bit 1: concurrent MMAs.
+extern "C" int nrf_dbg_tmem_rate(int warps, int reps, int mode, int grid, void* out, nrf_stream_t stream) {
+  NRF_REQUIRE(out && (warps == 4 || warps == 8 || warps == 16) && reps >= 1 && grid >= 1, "nrf_dbg_tmem_rate: bad args");
+  const size_t smem_bytes = 2 * 32768;
+  NRF_CUDA(cudaFuncSetAttribute(tmem_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  tmem_rate_kernel<<<grid, 64 + 16 * 32, smem_bytes, as_stream(stream)>>>(warps, reps, mode, static_cast<unsigned long long*>(out));
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

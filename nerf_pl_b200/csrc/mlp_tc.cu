@@ -36,14 +36,23 @@ constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreadsInfer = 64 + kEpiThreads;
 constexpr int kThreadsTrain = kThreadsInfer + 32;   // + the stash store warp
 constexpr uint32_t kTmemCols = 512;
-// Chunks per hand-over: the epilogue announces its output (fence.proxy.async + mbarrier arrive) every kGrp 64-column
-// chunks, and the MMAs of the next layer start per group.  1 = earliest start of the next layer but four fences per
-// layer, during which all epilogue warps of an SM sub-partition stall together; 2 measured best.
+// Hand-over groups: the epilogue announces its output (fence.proxy.async + mbarrier arrive) per GROUP of 64-column chunks,
+// and the MMAs of the next layer start per group.  NRF_FWD_GRP: 1 = {0}{1}{2}{3}, 2 = {0,1}{2,3}, 4 = {0,1,2,3},
+// 112 = {0}{1}{2,3}.  Every fence stalls all epilogue warps of an SM sub-partition together; measured on B200 (r02,
+// tools/step_probe.py): schemes 1, 2 and 112 are within 2 % of each other, 2 is kept.
 #ifndef NRF_FWD_GRP
 #define NRF_FWD_GRP 2
 #endif
-constexpr int kGrp = NRF_FWD_GRP;
-static_assert(kGrp == 1 || kGrp == 2 || kGrp == 4, "kGrp");
+constexpr int kGrpScheme = NRF_FWD_GRP;
+static_assert(kGrpScheme == 1 || kGrpScheme == 2 || kGrpScheme == 4 || kGrpScheme == 112, "NRF_FWD_GRP");
+// first / last chunk of the group chunk c belongs to; barriers and buffers are indexed by the group's LAST chunk
+__host__ __device__ constexpr int grp_first(int c) {
+  return kGrpScheme == 1 ? c : kGrpScheme == 2 ? (c & ~1) : kGrpScheme == 4 ? 0 : (c < 2 ? c : 2);
+}
+__host__ __device__ constexpr int grp_last(int c) {
+  return kGrpScheme == 1 ? c : kGrpScheme == 2 ? (c | 1) : kGrpScheme == 4 ? 3 : (c < 2 ? c : 3);
+}
+constexpr bool kSplit01 = grp_last(0) == 0;   // chunks 0 and 1 are handed over separately
 
 // shared-memory map (dynamic shared memory is declared 1024-byte aligned; no slack is left for re-alignment)
 constexpr uint32_t kSmEnc = 0;                                    // xyz encoding, later direction encoding
@@ -128,8 +137,11 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
     }
   } else if (warp == 1) {
     // ===================== UMMA issuer =====================
-    // One thread; descriptors are precomputed and only their 14-bit start-address field is advanced.
-    if (lane == 0) {
+    // The WHOLE warp runs this loop with warp-uniform values and one elected lane issues the tcgen05 instructions: the
+    // compiler then keeps descriptors and barrier addresses in uniform registers.  (Under `if (lane == 0)` every UTCHMMA
+    // was wrapped in a per-thread elect loop with R2UR moves, ~165 cycles per MMA: the issuing thread, not the tensor
+    // pipe (128 cycles per MMA), paced the kernel - tools/fwd_warp_skew.py.)
+    {
       uint32_t stage = 0, ph = 0;
       uint32_t a_par = 0;   // bit i: parity of the next completion of bar_a[i] to wait for
       long long w_a = 0, w_full = 0, t_begin = clock64();
@@ -140,11 +152,15 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
       const uint64_t ring_desc = make_desc_sw128(smem_u32(s_ring), 16, 1024);
       int mk = 0;   // (tile, layer) for the progress markers
       auto wait_a = [&](int src) {
-        const long long t0 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
+        const long long t0 = NRF_HEAVY ? clock64() : 0;
         NRF_MARK(1, 0x2000000 | (mk << 4) | src);
+#ifdef NRF_SPIN_MMA
+        mbar_wait_spin(bar_a + src, (a_par >> src) & 1u);
+#else
         mbar_wait(bar_a + src, (a_par >> src) & 1u);
+#endif
         a_par ^= 1u << src;
-        if (NRF_FWD_DEBUG && a.dbg) w_a += clock64() - t0;
+        if (NRF_HEAVY) w_a += clock64() - t0;
       };
       // Weight stages are awaited AHEAD of use, while the thread would otherwise idle waiting for the epilogue's
       // first chunk: the per-chunk critical path is then one barrier wait + the issue of 4 MMAs (K = 16 each).
@@ -158,17 +174,20 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
         }
       };
       auto chunk = [&](uint64_t a_desc, uint32_t d_tmem, uint32_t idesc, bool first) {
-        const long long t0 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
+        const long long t0 = NRF_HEAVY ? clock64() : 0;
         NRF_TRACE(1, tn1);
         NRF_MARK(1, 0x3000000 | (mk << 4));
         if (ready == 0) mbar_wait(bar_full + stage, ph); else --ready;
         NRF_TRACE(1, tn1);
-        if (NRF_FWD_DEBUG && a.dbg) w_full += clock64() - t0;
+        if (NRF_HEAVY) w_full += clock64() - t0;
         tc_fence_after();
         const uint64_t b_desc = ring_desc + (uint64_t)(stage * (kChunkBytes256 >> 4));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (!first || k) ? 1u : 0u);
-        umma_commit(bar_empty + stage);
+          for (int k = 0; k < 4; ++k) umma_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (!first || k) ? 1u : 0u);
+          umma_commit(bar_empty + stage);
+        }
+        __syncwarp();
         NRF_TRACE(1, tn1);
         if (++stage == kStages) { stage = 0; ph ^= 1; }
       };
@@ -176,6 +195,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
 #pragma unroll 1
         for (int L = 0; L < kLayers; ++L) {
           mk = (tile << 4) | L;
+          const bool mtr = NRF_FWD_DEBUG && blockIdx.x == 0 && lane == 0 && tile == 2 * (int)gridDim.x;
           const uint32_t d_tmem = tmem_base + (uint32_t)(L & 1) * 256;
           const uint32_t idesc = (L == 9) ? idesc128 : idesc256;
           bool first = true;
@@ -188,8 +208,11 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
             prewait(3);
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {
-              if (c % kGrp == 0) wait_a(c + kGrp - 1);
+              if (c == grp_first(c)) wait_a(grp_last(c));
+              if (c == 0) NRF_WTRACE(mtr, 16, L, 0);
+              if (c == grp_first(3)) NRF_WTRACE(mtr, 16, L, 2);
               chunk(act_desc + (uint64_t)(c * (kActChunkBytes >> 4)), d_tmem, idesc, first);
+              if (c == grp_last(0)) NRF_WTRACE(mtr, 16, L, 1);
               first = false;
             }
           }
@@ -197,10 +220,12 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
             wait_a(kBarDir);
             chunk(enc_desc, d_tmem, idesc, false);
           }
-          umma_commit(bar_acc + (L & 1));
+          if (elect_one()) umma_commit(bar_acc + (L & 1));
+          __syncwarp();
+          NRF_WTRACE(mtr, 16, L, 3);
         }
       }
-      if (NRF_FWD_DEBUG && a.dbg) {
+      if (NRF_FWD_DEBUG == 1 && a.dbg && lane == 0) {
         a.dbg[blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - t_begin);
         a.dbg[blockIdx.x * 8 + 1] = (unsigned long long)w_a;
         a.dbg[blockIdx.x * 8 + 2] = (unsigned long long)w_full;
@@ -281,12 +306,18 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
 #pragma unroll 1
       for (int L = 0; L < kLayers; ++L) {
         const uint32_t b = L & 1;
-        const long long tw0 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
+        const long long tw0 = NRF_HEAVY ? clock64() : 0;
         mk = (tile << 4) | L;
         if (lane == 0) NRF_MARK(warp, 0x5000000 | (mk << 4));
+#ifdef NRF_SPIN_EPI
+        mbar_wait_spin(bar_acc + b, (acc_par >> b) & 1u);
+#else
         mbar_wait(bar_acc + b, (acc_par >> b) & 1u);
-        if (NRF_FWD_DEBUG && a.dbg) w_acc += clock64() - tw0;
+#endif
+        if (NRF_HEAVY) w_acc += clock64() - tw0;
         if (et == 0) NRF_TRACE(2, tn2);
+        const bool wtr = NRF_FWD_DEBUG && blockIdx.x == 0 && lane == 0 && tile == 2 * (int)gridDim.x;
+        NRF_WTRACE(wtr, warp - 2, L, 0);
         acc_par ^= 1u << b;
         tc_fence_after();
         const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + b * 256;
@@ -305,7 +336,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
             if (c + 1 < 4) tmem_ld16(t_acc + (c + 1) * 64 + sub * 16, vn);
             const int c0 = c * 64 + sub * 16;
             const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-            if (c % kGrp == 0) acquire(c + kGrp - 1);
+            if (c == grp_first(c)) acquire(grp_last(c));
             if (L == 7) epi_fwd16<true, kTrain, true>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
             else if (L < 8) epi_fwd16<true, kTrain, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
             else epi_fwd16<false, false, false>(v, c0, bias_s, wsig_s, rsw, chunk_s, sub * 2, mreg, dot);
@@ -313,9 +344,11 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
               if (c == 1) mw0 = ~mreg; else mw1 = ~mreg;
               mreg = 0;
             }
-            if (c % kGrp == kGrp - 1) {
+            if (c == grp_last(c)) {
               if (feed) signal(c);             // the MMA thread (and, in training, the store warp) take it from here
               else if (kTrain) signal_store(c);
+              if (c == grp_last(0)) NRF_WTRACE(wtr, warp - 2, L, 1);
+              if (c == 3) NRF_WTRACE(wtr, warp - 2, L, 2);
             }
             if (et == 0) NRF_TRACE(2, tn2);
           }
@@ -369,10 +402,10 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
             }
             if (kTrain) {
               const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-              if (kGrp == 1 || c == 0) acquire(kGrp == 1 ? c : kGrp - 1);
+              if (kSplit01 || c == 0) acquire(kSplit01 ? c : grp_last(0));
               st_shared_v4(chunk_s + rsw.piece(sub * 2), pk[0], pk[1], pk[2], pk[3]);
               st_shared_v4(chunk_s + rsw.piece(sub * 2 + 1), pk[4], pk[5], pk[6], pk[7]);
-              if (kGrp == 1 || c == 1) signal_store(kGrp == 1 ? c : kGrp - 1);
+              if (kSplit01 || c == 1) signal_store(kSplit01 ? c : grp_last(0));
             }
           }
           if (kTrain) mask_tile[8 * 128 * 8 + (size_t)row * 4 + sub] = ~mreg;
@@ -390,7 +423,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
         }
       }
     }
-    if (NRF_FWD_DEBUG && a.dbg && et == 0) {
+    if (NRF_FWD_DEBUG == 1 && a.dbg && et == 0) {
       a.dbg[blockIdx.x * 8 + 4] = (unsigned long long)(clock64() - t_begin);
       a.dbg[blockIdx.x * 8 + 5] = (unsigned long long)w_acc;
     }
@@ -432,8 +465,9 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
         if (L < 9) {
           uint8_t* dst = a.stash + img_off(L < 8 ? kStashH0 + 4 * L : kStashFeat, 4, tile, a.num_tiles);
           const int bar0 = (L + 1 < kLayers) ? 0 : 8;
-          for (int c = 0; c < 4; c += kGrp)
-            store(bar0 + c + kGrp - 1, c + kGrp - 1, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes, kGrp * kActChunkBytes);
+          for (int c = 0; c < 4; c = grp_last(c) + 1)
+            store(bar0 + grp_last(c), grp_last(c), s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes,
+                  (uint32_t)(grp_last(c) - c + 1) * kActChunkBytes);
           if (L == 4) {
             if (kFull) store(kBarDir, kFreeEnc, s_enc, a.stash + img_off(kStashDir, 1, tile, a.num_tiles));
             else if (next < a.num_tiles) store(kBarEnc, kFreeEnc, s_enc, a.stash + img_off(kStashEnc, 1, next, a.num_tiles));
@@ -441,10 +475,10 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
         } else {
           if (next < a.num_tiles) store(kBarEnc, kFreeEnc, s_enc, a.stash + img_off(kStashEnc, 1, next, a.num_tiles));
           uint8_t* dst = a.stash + img_off(kStashMid, 2, tile, a.num_tiles);
-          if (kGrp == 1) {
+          if (kSplit01) {
             for (int c = 0; c < 2; ++c) store(8 + c, c, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes);
           } else {
-            store(8 + kGrp - 1, kGrp - 1, s_act, dst, 2 * kActChunkBytes);
+            store(8 + grp_last(0), grp_last(0), s_act, dst, 2 * kActChunkBytes);
           }
         }
       }

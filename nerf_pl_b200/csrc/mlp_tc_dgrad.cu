@@ -52,12 +52,19 @@ constexpr int kDgNumBarFree = 5;               // same buffers: the G-image stor
 // G0 (nobody but the store warp reads it) is announced on barriers of its own: a parity wait only tells "one completion
 // behind" from "up to date", so every waiter must consume every completion of a barrier
 constexpr int kDgNumBarS = 4;
-// chunks per hand-over (see kGrp in mlp_tc.cu)
+// hand-over groups of a layer's four chunks (see NRF_FWD_GRP in mlp_tc.cu): 1 = {0}{1}{2}{3}, 2 = {0,1}{2,3}, 4 = all,
+// 112 = {0}{1}{2,3}
 #ifndef NRF_DG_GRP
 #define NRF_DG_GRP 2
 #endif
-constexpr int kDgGrp = NRF_DG_GRP;
-static_assert(kDgGrp == 1 || kDgGrp == 2 || kDgGrp == 4, "kDgGrp");
+constexpr int kDgScheme = NRF_DG_GRP;
+static_assert(kDgScheme == 1 || kDgScheme == 2 || kDgScheme == 4 || kDgScheme == 112, "NRF_DG_GRP");
+__host__ __device__ constexpr int dg_first(int c) {
+  return kDgScheme == 1 ? c : kDgScheme == 2 ? (c & ~1) : kDgScheme == 4 ? 0 : (c < 2 ? c : 2);
+}
+__host__ __device__ constexpr int dg_last(int c) {
+  return kDgScheme == 1 ? c : kDgScheme == 2 ? (c | 1) : kDgScheme == 4 ? 3 : (c < 2 ? c : 3);
+}
 
 template <bool kFull>
 __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_constant__ DgradArgs a) {
@@ -115,7 +122,8 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // the whole warp runs the loop with warp-uniform values; one elected lane issues the tcgen05 instructions (see mlp_tc.cu)
+    {
       uint32_t stage = 0, ph = 0, a_par = 0, g = 0;   // g: running layer counter (accumulators alternate across tiles too)
       const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
       const uint64_t act_desc = make_desc_sw128(smem_u32(s_act), 16, 1024);
@@ -141,8 +149,8 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
 #pragma unroll 1
           for (int c = 0; c < nchunks; ++c) {
             const int src = from_pro ? kDgBarPro : c;
-            if (from_pro ? c == 0 : (c % kDgGrp == 0)) {
-              const int b = from_pro ? src : c + kDgGrp - 1;
+            if (from_pro ? c == 0 : (c == dg_first(c))) {
+              const int b = from_pro ? src : dg_last(c);
               mbar_wait(bar_a + b, (a_par >> b) & 1u);
               a_par ^= 1u << b;
             }
@@ -150,12 +158,16 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
             tc_fence_after();
             const uint64_t a_desc = (from_pro ? pro_desc : act_desc) + (uint64_t)(c * (kActChunkBytes >> 4));
             const uint64_t b_desc = ring_desc + (uint64_t)(stage * (kChunkBytes256 >> 4));
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (c | k) != 0);
-            umma_commit(bar_empty + stage);
+              for (int k = 0; k < 4; ++k) umma_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (c | k) != 0);
+              umma_commit(bar_empty + stage);
+            }
+            __syncwarp();
             if (++stage == kDgStages) { stage = 0; ph ^= 1; }
           }
-          umma_commit(bar_acc + (g & 1u));
+          if (elect_one()) umma_commit(bar_acc + (g & 1u));
+          __syncwarp();
         }
       }
     }
@@ -243,10 +255,10 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
             pk[(j >> 1) + 1] = cvt_bf16x2(f2, f3);
           }
           const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
-          if (c % kDgGrp == 0) acquire(c + kDgGrp - 1);
+          if (c == dg_first(c)) acquire(dg_last(c));
           st_shared_v4(chunk_s + rsw.piece(sub * 2), pk[0], pk[1], pk[2], pk[3]);
           st_shared_v4(chunk_s + rsw.piece(sub * 2 + 1), pk[4], pk[5], pk[6], pk[7]);
-          if (c % kDgGrp == kDgGrp - 1) signal(c);
+          if (c == dg_last(c)) signal(c);
         }
       }
       return dsig;
@@ -284,11 +296,11 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
           const int c0 = c * 64 + sub * 16;
           const uint32_t chunk_s = act_s + (uint32_t)c * kActChunkBytes;
           const uint32_t m = (c < 2) ? mw.x : mw.y;
-          if (c % kDgGrp == 0) acquire(c + kDgGrp - 1);
+          if (c == dg_first(c)) acquire(dg_last(c));
           if (kFull && t == 7) epi_dgrad16<true>(v, c, c0, m, dsig, wsig_s, rsw, chunk_s, sub * 2);
           else epi_dgrad16<false>(v, c, c0, m, dsig, wsig_s, rsw, chunk_s, sub * 2);
-          if (c % kDgGrp != kDgGrp - 1) {
-            // hand-over per group of kDgGrp chunks
+          if (c != dg_last(c)) {
+            // hand-over per group of chunks
           } else if (t > 0) {
             signal(c);   // the UMMA issuer and the store warp take it from here
           } else {       // G0: the store warp only
@@ -330,8 +342,9 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
     };
     auto store_act = [&](int slot, int tile) {
       uint8_t* dst = a.gstash + img_off(slot, 4, tile, a.num_tiles);
-      for (int c = 0; c < 4; c += kDgGrp)
-        store(c + kDgGrp - 1, slot == 0, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes, kDgGrp * kActChunkBytes);
+      for (int c = 0; c < 4; c = dg_last(c) + 1)
+        store(dg_last(c), slot == 0, s_act + c * kActChunkBytes, dst + (size_t)c * kActChunkBytes,
+              (uint32_t)(dg_last(c) - c + 1) * kActChunkBytes);
     };
     int tile = blockIdx.x;
     if (kFull && tile < a.num_tiles)

@@ -26,9 +26,13 @@ struct FwdArgs {
 #endif
 // Debug timeline (CTA 0 only, when dbg != null): dbg[kTraceBase + role * kTraceCap + n] = clock64() of event n.
 constexpr int kTraceBase = 148 * 8, kTraceCap = 4096;
+// dbg_flags bit 4 (16): LIGHT mode - only the NRF_WTRACE points are recorded (a clock read + one store each), so that the
+// timeline is not stretched by the counters / event traces below
+// NRF_FWD_DEBUG=2 compiles ONLY the light trace points in (the heavy counters alone slow the kernel by ~30 %).
+#define NRF_HEAVY (NRF_FWD_DEBUG == 1 && a.dbg && !(a.dbg_flags & 16))
 #define NRF_TRACE(role, n)                                                                          \
   do {                                                                                              \
-    if (NRF_FWD_DEBUG && a.dbg && blockIdx.x == 0 && (n) < kTraceCap) a.dbg[kTraceBase + (role) * kTraceCap + (n)++] = clock64(); \
+    if (NRF_HEAVY && blockIdx.x == 0 && (n) < kTraceCap) a.dbg[kTraceBase + (role) * kTraceCap + (n)++] = clock64(); \
   } while (0)
 
 // Progress markers (debug build, dbg = PINNED HOST memory so that they survive a trapped launch): the last wait every
@@ -36,9 +40,18 @@ constexpr int kTraceBase = 148 * 8, kTraceCap = 4096;
 constexpr int kMarkBase = kTraceBase + 4 * kTraceCap;
 #define NRF_MARK(slot, code)                                                                        \
   do {                                                                                              \
-    if (NRF_FWD_DEBUG && a.dbg) ((volatile unsigned long long*)a.dbg)[kMarkBase + blockIdx.x * 32 + (slot)] = (unsigned long long)(code); \
+    if (NRF_HEAVY) ((volatile unsigned long long*)a.dbg)[kMarkBase + blockIdx.x * 32 + (slot)] = (unsigned long long)(code); \
   } while (0)
 
+
+// Per-warp epilogue timeline (debug build, CTA 0, its third tile): dbg[kWarpBase + epilogue_warp * 64 + layer * 4 + e],
+// e = 0 accumulator seen complete, 1 / 2 first / last hand-over done.  Row 16 = the UMMA issuer: e = 0 first A operand
+// of the layer seen, 1 first group's MMAs issued, 2 last A operand seen, 3 accumulator commit issued  (tools/fwd_warp_skew.py)
+constexpr int kWarpBase = kMarkBase + 148 * 32;
+#define NRF_WTRACE(on, ew, layer, e)                                                                \
+  do {                                                                                              \
+    if (NRF_FWD_DEBUG && a.dbg && (on)) a.dbg[kWarpBase + (ew) * 64 + (layer) * 4 + (e)] = clock64(); \
+  } while (0)
 
 // CTA-pair forward (mlp_tc_pair.cu)
 int launch_fwd_pair(bool full, bool train, const FwdArgs& a, cudaStream_t st);
