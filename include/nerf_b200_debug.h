@@ -22,6 +22,7 @@ int nrf_dbg_stream(const void* base, unsigned long long cta_stride, unsigned lon
 /* Measurement aid: `grid` CTAs each issue `reps` tcgen05.mma (M=128, N=256, K=16, bf16) back to back; out[cta] (u64,
  * device) = cycles from the first issue to the completion of the last. */
 int nrf_dbg_mma_rate(int reps, int grid, void* out, nrf_stream_t stream);
+int nrf_dbg_mma_rate_n(int reps, int n_cols, int grid, void* out, nrf_stream_t stream);   /* the same with N = n_cols */
 /* Measurement aid: `grid` CTAs each bulk-store steps x piece bytes from shared memory to dst + cta * cta_stride with
  * `depth` (1, 2 or 4) stores in flight; out[cta] (u64, device) = cycles. */
 int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint32_t piece, int steps, int depth, int grid, void* out,

@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(32, 1) store_rate_kernel(uint8_t* dst, unsigne
 
 // Measurement aid: cycles per tcgen05.mma (kind::f16, M=128, N=256, K=16, operands from shared memory) when ONE
 // thread issues `reps` of them back to back into two alternating accumulators; out[cta] = total cycles.
-__global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, unsigned long long* out) {
+__global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, int n_cols, unsigned long long* out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 2 * 32768);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar + 1);
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, unsigned long
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
   if (threadIdx.x == 0) {
-    const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
+    const uint32_t idesc = make_idesc_bf16(128, n_cols, 0, 0);
     const uint64_t a_desc = make_desc_sw128(smem_u32(smem), 16, 1024);
     const uint64_t b_desc = make_desc_sw128(smem_u32(smem + 32768), 16, 1024);
     const long long t0 = clock64();
@@ -204,6 +204,7 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) tmem_rate_kernel(int warps, i
 
 using namespace nrf;
 using namespace nrf::tc;
+extern "C" int nrf_dbg_mma_rate_n(int reps, int n_cols, int grid, void* out, nrf_stream_t stream);
 
 // Launches `grid` CTAs; returns NRF_OK.  Total bytes moved = grid * steps * n_streams * piece.
 extern "C" int nrf_dbg_stream(const void* base, unsigned long long cta_stride, unsigned long long stream_stride,
@@ -221,11 +222,14 @@ extern "C" int nrf_dbg_stream(const void* base, unsigned long long cta_stride, u
 }
 
 // Launches `grid` CTAs issuing `reps` MMAs each; out (grid x u64, device) receives the cycles each CTA needed.
-extern "C" int nrf_dbg_mma_rate(int reps, int grid, void* out, nrf_stream_t stream) {
-  NRF_REQUIRE(out && reps >= 2 && grid >= 1, "nrf_dbg_mma_rate: bad args");
+extern "C" int nrf_dbg_mma_rate(int reps, int grid, void* out, nrf_stream_t stream) { return nrf_dbg_mma_rate_n(reps, 256, grid, out, stream); }
+
+// the same with N = n_cols (16..256, multiple of 16)
+extern "C" int nrf_dbg_mma_rate_n(int reps, int n_cols, int grid, void* out, nrf_stream_t stream) {
+  NRF_REQUIRE(out && reps >= 2 && grid >= 1 && n_cols >= 16 && n_cols <= 256 && n_cols % 16 == 0, "nrf_dbg_mma_rate: bad args");
   const size_t smem_bytes = 2 * 32768 + 64;
   NRF_CUDA(cudaFuncSetAttribute(mma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-  mma_rate_kernel<<<grid, 64, smem_bytes, as_stream(stream)>>>(reps, static_cast<unsigned long long*>(out));
+  mma_rate_kernel<<<grid, 64, smem_bytes, as_stream(stream)>>>(reps, n_cols, static_cast<unsigned long long*>(out));
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

@@ -22,3 +22,12 @@ for grid in (1, 148):
         flop = 2.0 * 128 * 256 * 16 * reps * grid
         print(f"grid={grid:3d} reps={reps:5d}: {cyc / reps:7.1f} cycles per MMA  ({2 * 128 * 256 * 16 / (cyc / reps):.0f} FLOP/clk/SM), "
               f"kernel {ms:.3f} ms -> {flop / ms / 1e9:.0f} TFLOP/s, implied clock {cyc / ms / 1e3:.0f} MHz", flush=True)
+
+print("N sweep (148 CTAs, 4096 MMAs each): cycles per MMA and per 256 output columns")
+for n in (256, 128, 64, 32):
+    out = torch.zeros(148, dtype=torch.int64, device=dev)
+    for _ in range(2):
+        _lib.call("nrf_dbg_mma_rate_n", 4096, n, 148, out.data_ptr(), None)
+    torch.cuda.synchronize()
+    cyc = out.double().mean().item() / 4096
+    print(f"N={n:3d}: {cyc:6.1f} cycles per MMA = {cyc * 256 / n:6.1f} per 256 columns ({2 * 128 * n * 16 / cyc:.0f} FLOP/clk/SM)", flush=True)
