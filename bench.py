@@ -648,6 +648,9 @@ def run_gpu(args):
                 "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD,
                            "rays_per_gpu": B, "parallelism": f"ray-sharded dp{world}",
+                           "gradient_exchange": ("none (one GPU)" if world == 1 else
+                                                 "nrf_peer_allreduce_mean: one kernel per rank over NVLink peer memory (CUDA IPC), "
+                                                 "captured in the step's graph" if bucket.peer is not None else "NCCL all-reduce"),
                            "l2": "256 MB flush between timed steps; per-step activation traffic >> 126 MB L2",
                            "launch": "whole step replayed as one CUDA graph (nerf_pl_b200.graph.GraphedStep)",
                            "train_step_flop_per_ray": FLOP_PER_RAY_TRAIN,
@@ -702,7 +705,8 @@ def run_gpu(args):
                                 f"B200, {B} rays per step, fwd+bwd+Adam, wall clock with a sync per step, median of 5")
             line["cpu_baseline"]["torch_cuda_same_gpu"] = same_gpu
         emit(line)
-    graphed.close()          # before the process group goes away: the graph holds a captured NCCL all-reduce
+    graphed.close()          # before the process group goes away: the graph holds the captured gradient exchange
+    bucket.close()           # unmap the peers' gradient buffers (collective)
     if world > 1:
         dist.barrier()
         torch.cuda.synchronize()

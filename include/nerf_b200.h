@@ -273,6 +273,34 @@ int nrf_light_scatter(const float* g_wlb, const int* gidx, int64_t n, int64_t n_
 int nrf_w_mapping(const float* pixels, const float* value, const float* M, int64_t n, float eps, float* out,
                   nrf_stream_t stream);
 
+/* (e) Gradient exchange of the ray-sharded training step over NVLink peer memory - replaces the NCCL all-reduce that
+ * DistributedDataParallel issues for the reference (train.py:174-175).  The flat fp32 gradient buffer of every
+ * rank is a cudaMalloc allocation shared with the other ranks' processes through CUDA IPC:
+ *   nrf_peer_alloc / nrf_peer_free      zero-filled device allocation owned by this process
+ *   nrf_peer_export                     64-byte IPC handle of an allocation (cudaIpcGetMemHandle)
+ *   nrf_peer_import / nrf_peer_close    map a peer's allocation into this process (peer access enabled lazily)
+ *   nrf_peer_allreduce_mean             bufs[q][0..n) <- mean over q of bufs[q][0..n), in place, in every rank's buffer:
+ *                                       ONE launch per rank; rank r reduces slice r in rank order 0..world-1 (all ranks end
+ *                                       up bit-identical) and stores it into all buffers; two flag barriers in the peers'
+ *                                       memory (flags[q]: world words of rank q, written by the peers; seq / counter: this
+ *                                       rank's round number and CTA counter, zero-initialised).  Every rank must call it the
+ *                                       same number of times; capturable in a CUDA graph. */
+#define NRF_PEER_MAX 8
+typedef struct {
+  void* bufs[NRF_PEER_MAX];    /* gradient buffer of every rank, as mapped in THIS process */
+  void* flags[NRF_PEER_MAX];   /* flag words of every rank (>= NRF_PEER_MAX x 4 bytes each), as mapped in this process */
+  int32_t rank, world;
+  int64_t n;                   /* fp32 elements */
+  void* seq;                   /* this rank: 4 bytes, round number */
+  void* counter;               /* this rank: 4 bytes, CTA counter */
+} nrf_peer_comm;
+int nrf_peer_alloc(size_t bytes, void** ptr);
+int nrf_peer_free(void* ptr);
+int nrf_peer_export(const void* ptr, void* handle64);
+int nrf_peer_import(const void* handle64, void** ptr);
+int nrf_peer_close(void* ptr);
+int nrf_peer_allreduce_mean(const nrf_peer_comm* comm, nrf_stream_t stream);
+
 /* Diagnostics and microbenchmarks are NOT part of this library: they are compiled only with NRF_DEBUG_BUILD=1 and
  * declared in include/nerf_b200_debug.h. */
 

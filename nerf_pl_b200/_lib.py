@@ -76,6 +76,21 @@ SIGNATURES = {
     "nrf_shadow_bwd": (I, [P, P, P, P, P, P, P, P, P, L, I, I, I, F, F, F, F, I, P, P, P, P, Z, P]),
 }
 
+class PeerComm(ctypes.Structure):
+    """nrf_peer_comm (include/nerf_b200.h)."""
+    _fields_ = [("bufs", ctypes.c_void_p * 8), ("flags", ctypes.c_void_p * 8), ("rank", ctypes.c_int32),
+                ("world", ctypes.c_int32), ("n", ctypes.c_int64), ("seq", ctypes.c_void_p), ("counter", ctypes.c_void_p)]
+
+
+SIGNATURES.update({
+    "nrf_peer_alloc": (I, [Z, ctypes.POINTER(ctypes.c_void_p)]),
+    "nrf_peer_free": (I, [P]),
+    "nrf_peer_export": (I, [P, P]),
+    "nrf_peer_import": (I, [P, ctypes.POINTER(ctypes.c_void_p)]),
+    "nrf_peer_close": (I, [P]),
+    "nrf_peer_allreduce_mean": (I, [ctypes.POINTER(PeerComm), P]),
+})
+
 # include/nerf_b200_debug.h: present only in a library built with NRF_DEBUG_BUILD=1 (tools/ microbenchmarks)
 DEBUG_SIGNATURES = {
     "nrf_dbg_set_counters": (None, [P]),

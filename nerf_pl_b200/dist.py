@@ -2,6 +2,10 @@
 exchange is ONE flat all-reduce of the MLP gradients (2 x 595 844 fp32 = 4.77 MB) over NCCL/NVLink in
 training, and one gather of the per-ray outputs for full-frame renders.  Works with gloo on CPU for the
 host-logic tests."""
+import ctypes
+import os
+import socket
+
 import torch
 import torch.distributed as dist
 
@@ -13,18 +17,121 @@ def shard_bounds(n_items: int, rank: int, world: int):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+class _DevMem:
+    """torch view of a raw device allocation (CUDA array interface, zero copy)."""
+
+    def __init__(self, ptr, n_floats):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+class PeerExchange:
+    """The flat gradient buffers of all ranks of ONE node mapped into every rank's process (CUDA IPC over NVLink peer
+    access), for nrf_peer_allreduce_mean (csrc/peer_allreduce.cu): the training step's only collective as one kernel
+    launch per rank that loads / stores the peers' memory directly.  Collective constructor (every rank of `group`
+    must call it); `ok` is False on every rank alike when any rank cannot take part (ranks on several hosts, more than
+    8 ranks, no CUDA, IPC refused), and the caller keeps NCCL."""
+
+    def __init__(self, n_floats, device, group=None):
+        from . import _lib
+        self.ok, self.n, self.device = False, int(n_floats), device
+        self.own, self.mapped, self.flat = [], [], None
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        usable = (device.type == "cuda" and 2 <= world <= 8 and "nccl" in str(dist.get_backend(group))
+                  and os.environ.get("NRF_PEER_ALLREDUCE", "1") != "0")
+        hosts = [None] * world
+        dist.all_gather_object(hosts, (socket.gethostname(), bool(usable)), group=group)
+        if len({h for h, _ in hosts}) != 1 or not all(u for _, u in hosts):
+            return
+        lib = _lib.load()
+        err = ""
+        handles = None
+        try:
+            with torch.cuda.device(device):
+                buf, flg = ctypes.c_void_p(), ctypes.c_void_p()
+                _lib.call("nrf_peer_alloc", self.n * 4, ctypes.byref(buf))
+                self.own.append(buf.value)
+                _lib.call("nrf_peer_alloc", 256, ctypes.byref(flg))      # 8 flag words, then seq (+64) and counter (+128)
+                self.own.append(flg.value)
+                hb, hf = ctypes.create_string_buffer(64), ctypes.create_string_buffer(64)
+                _lib.call("nrf_peer_export", buf.value, hb)
+                _lib.call("nrf_peer_export", flg.value, hf)
+                handles = (hb.raw, hf.raw)
+        except Exception as e:      # noqa: BLE001  (every rank must reach the collectives below)
+            err = f"{type(e).__name__}: {e}"
+        everyone = [None] * world
+        dist.all_gather_object(everyone, (handles, err), group=group)
+        good = all(h is not None for h, _ in everyone)
+        comm = _lib.PeerComm()
+        if good:
+            try:
+                with torch.cuda.device(device):
+                    for q, (h, _) in enumerate(everyone):
+                        if q == rank:
+                            comm.bufs[q], comm.flags[q] = self.own[0], self.own[1]
+                            continue
+                        pb, pf = ctypes.c_void_p(), ctypes.c_void_p()
+                        _lib.call("nrf_peer_import", h[0], ctypes.byref(pb))
+                        self.mapped.append(pb.value)
+                        _lib.call("nrf_peer_import", h[1], ctypes.byref(pf))
+                        self.mapped.append(pf.value)
+                        comm.bufs[q], comm.flags[q] = pb.value, pf.value
+            except Exception as e:      # noqa: BLE001
+                good, err = False, f"{type(e).__name__}: {e}"
+        flags = [None] * world
+        dist.all_gather_object(flags, (bool(good), err), group=group)
+        if not all(g for g, _ in flags):
+            self.error = "; ".join(e for _, e in flags if e)
+            self.close()
+            return
+        comm.rank, comm.world, comm.n = rank, world, self.n
+        comm.seq, comm.counter = self.own[1] + 64, self.own[1] + 128
+        self.comm = comm
+        self.flat = torch.as_tensor(_DevMem(self.own[0], self.n), device=device)
+        self.ok = True
+
+    def allreduce_mean(self):
+        from . import _lib
+        from .ops import _stream
+        with torch.cuda.device(self.device):
+            _lib.call("nrf_peer_allreduce_mean", ctypes.byref(self.comm), _stream())
+
+    def close(self):
+        """Unmap the peers' buffers and free this rank's (after a barrier: nobody may still be reading them)."""
+        from . import _lib
+        if not (self.own or self.mapped):
+            return
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        for ptr in self.mapped:
+            _lib.call("nrf_peer_close", ptr)
+        self.mapped = []
+        if self.ok and dist.is_initialized():
+            dist.barrier()
+        for ptr in self.own:
+            _lib.call("nrf_peer_free", ptr)
+        self.own, self.ok, self.flat = [], False, None
+
+
 class GradBucket:
-    """One flat fp32 buffer aliasing every parameter's .grad, so the gradient all-reduce is a single
-    collective launch (latency-bound at 4.77 MB; NVSwitch makes it ~tens of microseconds).
+    """One flat fp32 buffer aliasing every parameter's .grad, so the gradient exchange of the ray-sharded training step
+    is a single launch: `nrf_peer_allreduce_mean` over NVLink peer memory when all ranks share a node (PeerExchange
+    above; `peer=False` or NRF_PEER_ALLREDUCE=0 keeps NCCL), one NCCL all-reduce otherwise (gloo on CPU for the
+    host-logic tests).
 
     NeRF modules are also told where their gradients live (`_nrf_grad_sinks`): the fused render pass then lets its
     backward kernels add into the bucket directly instead of handing zero-initialised temporaries to autograd
     (mlp.backward_rays), as long as the parameters' .grad still are the bucket's views."""
 
-    def __init__(self, modules):
+    def __init__(self, modules, peer=True, group=None):
         self.params = [p for m in modules for p in m.parameters() if p.requires_grad]
         n = sum(p.numel() for p in self.params)
-        self.flat = torch.zeros(n, dtype=torch.float32, device=self.params[0].device)
+        self.peer = None
+        dev = self.params[0].device
+        if peer and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1 and dev.type == "cuda":
+            px = PeerExchange(n, dev, group)      # collective: every rank decides alike
+            if px.ok:
+                self.peer = px
+        self.flat = self.peer.flat if self.peer is not None else torch.zeros(n, dtype=torch.float32, device=dev)
         off = 0
         for p in self.params:
             p.grad = self.flat[off:off + p.numel()].view_as(p)
@@ -39,8 +146,20 @@ class GradBucket:
     def allreduce_mean(self, group=None, async_op=False):
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return None
+        if self.peer is not None:
+            self.peer.allreduce_mean()
+            return None
         self.flat.div_(dist.get_world_size(group))
         return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+    def close(self):
+        """Release the peer mapping (call before torch.distributed.destroy_process_group())."""
+        if self.peer is not None:
+            for p in self.params:
+                p.grad = None
+            self.flat = None
+            self.peer.close()
+            self.peer = None
 
 
 def render_sharded(render_fn, rays, group=None, gather_dst=0):
