@@ -223,6 +223,22 @@ int nrf_shadow_fwd(const float* cam_pixels, const float* cam_depth, const float*
                    const float* light_pixels, const float* light_depth, int64_t n, int res_w, int res_h,
                    int mode, float delta, float epsilon, float new_min, float new_max, int sigmoid,
                    float out_bias, float* out, void* workspace, size_t workspace_bytes, nrf_stream_t stream);
+/* nrf_shadow_fwd without a workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, arithmetic and output as nrf_shadow_fwd; the scratch is a file-scope
+ * `static __device__` array in shadow.cu sized for one config-5 batch - at most NRF_SHADOW_STATIC_MAX_RAYS camera rays
+ * against a light map of at most NRF_SHADOW_STATIC_MAX_TEXELS texels (368 KB, held by every GPU that loads the library
+ * until exit); larger sizes return NRF_ERR_WORKSPACE with a message and launch nothing.  The call performs no cudaMalloc /
+ * cudaFree (its device address is looked up once per device with cudaGetSymbolAddress).  All calls on a device share the
+ * one array, which keeps the previous call's contents (every word read is rewritten first, nothing relies on zeros):
+ * calls that overlap on the GPU (two streams, two host threads) race - serialise them on one stream. */
+#define NRF_SHADOW_STATIC_MAX_RAYS 4096
+#define NRF_SHADOW_STATIC_MAX_TEXELS 16384
+int nrf_shadow_fwd_static(const float* cam_pixels, const float* cam_depth, const float* cam_M, const float* cam_eye,
+                          const float* light_Minv, const float* light_M, const float* light_eye,
+                          const float* light_pixels, const float* light_depth, int64_t n, int res_w, int res_h,
+                          int mode, float delta, float epsilon, float new_min, float new_max, int sigmoid,
+                          float out_bias, float* out, nrf_stream_t stream);
 /* g_out (n,3) -> g_cam_depth (n) (overwritten), g_light_depth (W*H) (ACCUMULATED, may be NULL). */
 int nrf_shadow_bwd(const float* cam_pixels, const float* cam_depth, const float* cam_M, const float* cam_eye,
                    const float* light_Minv, const float* light_M, const float* light_eye,

@@ -65,6 +65,7 @@ SIGNATURES = {
     "nrf_mlp_tc_bwd": (I, [P, PG, P, P, L, I, I, P, P, P, P, Z, P, Z, P]),
     "nrf_shadow_workspace_bytes": (Z, [L, L]),
     "nrf_shadow_fwd": (I, [P, P, P, P, P, P, P, P, P, L, I, I, I, F, F, F, F, I, F, P, P, Z, P]),
+    "nrf_shadow_fwd_static": (I, [P, P, P, P, P, P, P, P, P, L, I, I, I, F, F, F, F, I, F, P, P]),
     "nrf_normed_w": (I, [P, P, P, P, L, P, P]),
     "nrf_project_to_light": (I, [P, P, P, P, L, P, P, L, I, P, P, P, P]),
     "nrf_shadow_map_workspace_bytes": (Z, []),

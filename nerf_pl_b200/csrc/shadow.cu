@@ -9,6 +9,7 @@
 // Backward recomputes k0-k2 and adds the reductions autograd performs for min()/max().
 // HBM-bound, tiny: ~100 B per camera ray.
 #include <cfloat>
+#include <mutex>
 #include "common.cuh"
 
 namespace nrf {
@@ -326,6 +327,72 @@ extern "C" int nrf_shadow_fwd(const float* cam_pixels, const float* cam_depth, c
   NRF_REQUIRE(out != nullptr, "nrf_shadow_fwd: null output");
   cudaStream_t st = as_stream(stream);
   const ShadowWs w = carve(workspace, n, (int64_t)res_w * res_h);
+  rc = shadow_common(cam_pixels, cam_depth, cam_M, cam_eye, light_Minv, light_M, light_eye, light_pixels, light_depth,
+                     n, res_w, res_h, mode, w, st);
+  if (rc) return rc;
+  const ShadowCfg cfg{mode, sigmoid, delta, epsilon, new_min, new_max, out_bias};
+  shade_kernel<<<sgrid(n), 256, 0, st>>>(w.diff, w.seg_start, w.seg_min, w.seg_max, n, cfg, out);
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// nrf_shadow_fwd_static: the same four launches with the scratch in a file-scope device array instead of a caller
+// workspace, for callers that may not allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// Sized for one config-5 batch: NRF_SHADOW_STATIC_MAX_RAYS camera rays against a light map of
+// NRF_SHADOW_STATIC_MAX_TEXELS texels.  Every GPU that loads the library holds the array until exit.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace nrf {
+constexpr size_t cup256(size_t v) { return (v + 255) & ~size_t(255); }
+// mirrors carve(): 3 light-map arrays + 11 per-ray arrays, each rounded up to 256 bytes
+constexpr size_t kShadowStaticBytes = 3 * cup256((size_t)NRF_SHADOW_STATIC_MAX_TEXELS * 4) +
+                                      11 * cup256((size_t)NRF_SHADOW_STATIC_MAX_RAYS * 4);
+static __device__ __align__(256) unsigned char g_shadow_static_scratch[kShadowStaticBytes];
+
+// In host code `g_shadow_static_scratch` is only a stand-in for the symbol: its device address is looked up once per
+// device, with that device current, and cached.
+static int shadow_static_ptr(void** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static void* ptrs[kMaxDev] = {};
+  int dev = -1;
+  NRF_CUDA(cudaGetDevice(&dev));
+  NRF_REQUIRE(dev >= 0 && dev < kMaxDev, "nrf_shadow_fwd_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    NRF_CUDA(cudaGetSymbolAddress(&p, g_shadow_static_scratch));
+    NRF_REQUIRE(p != nullptr, "nrf_shadow_fwd_static: no device address for the static scratch");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return NRF_OK;
+}
+}  // namespace nrf
+
+extern "C" int nrf_shadow_fwd_static(const float* cam_pixels, const float* cam_depth, const float* cam_M,
+                                     const float* cam_eye, const float* light_Minv, const float* light_M,
+                                     const float* light_eye, const float* light_pixels, const float* light_depth,
+                                     int64_t n, int res_w, int res_h, int mode, float delta, float epsilon,
+                                     float new_min, float new_max, int sigmoid, float out_bias, float* out,
+                                     nrf_stream_t stream) {
+  if (n > (int64_t)NRF_SHADOW_STATIC_MAX_RAYS || (int64_t)res_w * res_h > (int64_t)NRF_SHADOW_STATIC_MAX_TEXELS) {
+    set_error("nrf_shadow_fwd_static: %lld rays / %lld light texels exceed the static scratch (at most %d rays, %d texels); "
+              "use nrf_shadow_fwd with a caller workspace", (long long)n, (long long)res_w * res_h,
+              NRF_SHADOW_STATIC_MAX_RAYS, NRF_SHADOW_STATIC_MAX_TEXELS);
+    return NRF_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  int rc = shadow_static_ptr(&scratch);
+  if (rc) return rc;
+  rc = shadow_check("nrf_shadow_fwd_static", cam_pixels, cam_depth, cam_M, cam_eye, light_Minv, light_M, light_eye,
+                    light_pixels, light_depth, n, res_w, res_h, mode, scratch, kShadowStaticBytes);
+  if (rc || n == 0) return rc;
+  NRF_REQUIRE(out != nullptr, "nrf_shadow_fwd_static: null output");
+  cudaStream_t st = as_stream(stream);
+  // nothing in the scratch has to start at zero: light_norm / segment / project overwrite every word the shade
+  // kernel reads (segment_kernel re-initialises the per-segment min / max keys), so the previous call's contents are dead
+  const ShadowWs w = carve(scratch, n, (int64_t)res_w * res_h);
   rc = shadow_common(cam_pixels, cam_depth, cam_M, cam_eye, light_Minv, light_M, light_eye, light_pixels, light_depth,
                      n, res_w, res_h, mode, w, st);
   if (rc) return rc;
