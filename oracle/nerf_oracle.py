@@ -527,6 +527,35 @@ def psnr(image_pred: Tensor, image_gt: Tensor, valid_mask: Optional[Tensor] = No
     return -10 * torch.log10(torch.mean(value))
 
 
+def ssim(image_pred: Tensor, image_gt: Tensor, reduction: str = "mean") -> Tensor:
+    """metrics.py:15-20: 1 - 2 * kornia.losses.ssim(pred, gt, 3, reduction).  kornia 0.2.0 (requirements.txt:5) is absent
+    here: PARITY UNPINNED.  Published algorithm restated with explicit window loops in float64: per channel, 3x3 Gaussian
+    window (sigma 1.5, normalised), zero padding, C1 = 0.01^2, C2 = 0.03^2, dssim = clamp(1 - ssim_map, 0, 1) / 2."""
+    a = image_pred.detach().double().numpy()
+    b = image_gt.detach().double().numpy()
+    g = np.exp(-np.array([-1.0, 0.0, 1.0]) ** 2 / (2 * 1.5 ** 2))
+    g /= g.sum()
+    win = np.outer(g, g)
+
+    def blur(x):
+        pad = np.pad(x, ((0, 0), (0, 0), (1, 1), (1, 1)))
+        out = np.zeros_like(x)
+        for dy in range(3):
+            for dx in range(3):
+                out += win[dy, dx] * pad[:, :, dy:dy + x.shape[2], dx:dx + x.shape[3]]
+        return out
+
+    mu1, mu2 = blur(a), blur(b)
+    s1, s2, s12 = blur(a * a) - mu1 ** 2, blur(b * b) - mu2 ** 2, blur(a * b) - mu1 * mu2
+    smap = ((2 * mu1 * mu2 + 1e-4) * (2 * s12 + 9e-4)) / ((mu1 ** 2 + mu2 ** 2 + 1e-4) * (s1 + s2 + 9e-4))
+    d = np.clip(1.0 - smap, 0.0, 1.0) / 2.0
+    if reduction == "mean":
+        d = d.mean()
+    elif reduction == "sum":
+        d = d.sum()
+    return torch.as_tensor(1 - 2 * d)
+
+
 def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, step: int, lr: float,
               betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0):
     """One step of the optimizer utils/__init__.py:17-19 constructs: `Adam(parameters, lr, eps=1e-8, weight_decay)`.

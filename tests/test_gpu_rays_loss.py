@@ -109,3 +109,21 @@ def test_fused_mse_full_frame_deterministic(dev):
     np.testing.assert_allclose(metrics.psnr(ad, td).item(), -10 * np.log10(ref), rtol=1e-6)
     with pytest.raises(RuntimeError):
         losses.mse_pair(a, None, t)
+
+
+def test_ssim_vs_oracle(dev):
+    """metrics.py:15-20 (1 - 2 * kornia dssim, 3x3 Gaussian window): the device tensor-op version against the oracle's
+    explicit float64 window loops, all three reductions; identical images give exactly 1.  kornia 0.2.0 is absent from
+    this image, so both restate its published algorithm: parity unpinned."""
+    from nerf_pl_b200 import metrics
+    g = torch.Generator().manual_seed(9)
+    gt = torch.rand(1, 3, 37, 53, generator=g)
+    pred = (gt + 0.1 * torch.randn(1, 3, 37, 53, generator=g)).clamp(0, 1)
+    for red in ("mean", "sum", "none"):
+        ref = O.ssim(pred, gt, red).numpy()
+        got = metrics.ssim(pred.to(dev), gt.to(dev), red).cpu().numpy()
+        np.testing.assert_allclose(got, ref, rtol=1e-5 if red == "sum" else 0, atol=1e-4 if red != "sum" else 0)   # fp32 E[x^2] - mu^2
+    assert metrics.ssim(gt.to(dev), gt.to(dev)).item() == pytest.approx(1.0, abs=1e-6)
+    assert -1.0 <= metrics.ssim(pred.to(dev), gt.to(dev)).item() < 1.0
+    with pytest.raises(ValueError):
+        metrics.ssim(pred[0].to(dev), gt[0].to(dev))
