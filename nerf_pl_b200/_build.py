@@ -7,7 +7,7 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIBDIR = os.path.join(HERE, "lib")
+LIBDIR = os.environ.get("NRF_LIBDIR") or os.path.join(HERE, "lib")   # NRF_LIBDIR: experiment builds beside the product library
 LIB = os.path.join(LIBDIR, "libnerf_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 EXTRA = os.environ.get("NVCC_EXTRA", "").split()

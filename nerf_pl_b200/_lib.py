@@ -5,7 +5,7 @@ import os
 from ctypes import POINTER, Structure, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libnerf_b200.so")
+LIB_PATH = os.path.join(os.environ.get("NRF_LIBDIR") or os.path.join(_HERE, "lib"), "libnerf_b200.so")
 NRF_MAX_D = 16
 
 ERR_NAMES = {1: "invalid argument", 2: "CUDA error", 3: "unsupported", 4: "workspace too small"}

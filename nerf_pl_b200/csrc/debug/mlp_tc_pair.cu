@@ -29,6 +29,9 @@ namespace pair {
 #ifndef NRF_PAIR_HACK
 #define NRF_PAIR_HACK 0   // 1: timing experiment only (both slots share ONE enc buffer -> wrong results, frees a 4th stage)
 #endif
+#ifndef NRF_PAIR_SPIN
+#define NRF_PAIR_SPIN 0   // 1: the waits on the weight round trip (producer, relay, issuer) poll instead of suspending
+#endif
 constexpr int kStages = NRF_PAIR_HACK ? 4 : 3;
 constexpr uint32_t kEncStride = NRF_PAIR_HACK ? 0 : kActChunkBytes;
 constexpr uint32_t kHalfChunk = kChunkBytes256 / 2;   // 16 KB: this CTA's N half of a weight chunk
@@ -83,7 +86,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTrain ? kThreadsTra
 
   if (threadIdx.x == 0) {
     if (smem_u32(smem) & 1023u) __trap();
-    for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + s, rank == 0 ? 2 : 1); mbar_init(bar_empty + s, 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + s, (rank == 0 && !(a.dbg_flags & 8)) ? 2 : 1); mbar_init(bar_empty + s, 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(bar_a + s, 2 * kEpiWarps); mbar_init(bar_acc + s, 1); }
     for (int s = 0; s < kNumBuf; ++s) { mbar_init(bar_st + s, kEpiWarps); mbar_init(bar_free + s, 1); }
     fence_barrier_init();
@@ -115,7 +118,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTrain ? kThreadsTra
           for (int r = 0; r < reps; ++r) {
             for (int j = 0; j < nl; ++j) {
               NRF_MARK(0, 0x1000000 | (it << 12) | (L << 8) | (r << 4) | j);
-              mbar_wait(bar_empty + stage, ph ^ 1);
+              if (NRF_PAIR_SPIN) mbar_wait_spin(bar_empty + stage, ph ^ 1); else mbar_wait(bar_empty + stage, ph ^ 1);
               uint8_t* dst = s_ring + stage * kHalfChunk;
               if (L == 9) {   // N = 128: this CTA's half of a chunk is 8 KB; chunks 2j and 2j+1 (the last load: dir chunk only)
                 const uint8_t* src = blob + (size_t)(kFwdChunksSigma + 4) * kChunkBytes256 + (size_t)rank * (kChunkBytes128 / 2);
@@ -153,7 +156,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTrain ? kThreadsTra
           for (int slot = 0; slot < 2; ++slot) {
             NRF_MARK(1, 0x2000000 | (it << 12) | (L << 8) | (slot << 4));
             const long long t0 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
-            mbar_wait_cluster(bar_a + slot, (a_par >> slot) & 1u);
+            if (NRF_PAIR_SPIN) mbar_wait_cluster_spin(bar_a + slot, (a_par >> slot) & 1u); else mbar_wait_cluster(bar_a + slot, (a_par >> slot) & 1u);
             if (NRF_FWD_DEBUG && a.dbg) w_a += clock64() - t0;
             a_par ^= 1u << slot;
             tc_fence_after();
@@ -175,14 +178,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTrain ? kThreadsTra
               if (new_stage && (!shared || slot == 0)) {   // slot 1 of a shared layer re-walks stages slot 0 has seen
                 NRF_MARK(1, 0x3000000 | (it << 12) | (L << 8) | (slot << 4) | j);
                 const long long t1 = (NRF_FWD_DEBUG && a.dbg) ? clock64() : 0;
-                mbar_wait_cluster(bar_full + st, p);
+                if (NRF_PAIR_SPIN) mbar_wait_cluster_spin(bar_full + st, p); else mbar_wait_cluster(bar_full + st, p);
                 if (NRF_FWD_DEBUG && a.dbg) w_pfull += clock64() - t1;
                 tc_fence_after();
               }
               const uint64_t b_desc = ring_desc + (uint64_t)((st * kHalfChunk + ((L == 9 && (j & 1)) ? kChunkBytes128 / 2 : 0)) >> 4);
+              const int reps = (NRF_FWD_DEBUG && (a.dbg_flags & 32)) ? 4 : 1;   // timing experiment: every MMA issued 4 times
+              for (int rep = 0; rep < reps; ++rep)
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                if (!(NRF_FWD_DEBUG && (a.dbg_flags & 1))) umma_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (j | k) ? 1u : 0u);
+                if (!(NRF_FWD_DEBUG && (a.dbg_flags & 1))) umma_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (j | k | rep) ? 1u : 0u);
               if (last_of_stage) {
                 if (release) umma_commit_pair(bar_empty + st, 0x3);
                 if (++st == kStages) { st = 0; p ^= 1; }
@@ -206,7 +211,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTrain ? kThreadsTra
         a.dbg[blockIdx.x * 8 + 6] = (unsigned long long)w_mma;
         a.dbg[blockIdx.x * 8 + 7] = (unsigned long long)n_mma;
       }
-    } else if (lane == 0) {
+    } else if (lane == 0 && !(a.dbg_flags & 8)) {
       // ===================== relay (peer CTA): my half of the stage has landed -> leader =====================
       uint32_t stage = 0, ph = 0;
       for (int it = 0; iter_base(it) < a.num_tiles; ++it) {
@@ -214,7 +219,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTrain ? kThreadsTra
           const int n = (layer_shared(L) ? 1 : 2) * layer_loads(L);
           for (int j = 0; j < n; ++j) {
             NRF_MARK(1, 0x8000000 | (it << 12) | (L << 8) | j);
-            mbar_wait(bar_full + stage, ph);
+            if (NRF_PAIR_SPIN) mbar_wait_spin(bar_full + stage, ph); else mbar_wait(bar_full + stage, ph);
             mbar_arrive_cluster(mapa_u32(smem_u32(bar_full + stage), 0));
             if (++stage == kStages) { stage = 0; ph ^= 1; }
           }

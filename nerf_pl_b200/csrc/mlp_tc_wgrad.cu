@@ -63,8 +63,20 @@ struct WgradArgs {
   const float* dpre;           // (tiles*128, 4)
   float* dW_sigma; float* db_sigma; float* dW_rgb; float* db_rgb;
   int* counters;               // [n_jobs] next granule of each job, zeroed before launch
-  int dbg_flags;               // experiments only (NRF_DBG_FLAGS): 1 = skip side work, 2 = skip MMAs
+  int dbg_flags;               // experiments only (NRF_DBG_FLAGS): 1 = skip side work, 2 = skip MMAs, 4 = side loads without
+                               // arithmetic, 64 = skip the flush, 8192 = bias sums only, 16384 = head gradients only
 };
+
+// Head jobs (side 1: sigma head, side 2: rgb head) need per-row upstream gradients: d_sigma (rows) floats, dpre (rows, 4)
+// floats.  They travel in X slot 4 of the stage, which no head job uses for an image (b_n <= 4 there).
+constexpr uint32_t kWgSideVecOff = (kWgASlots + 4) * kWgSlice;
+__host__ __device__ inline uint32_t side_vec_bytes(int side) {
+  return side == 1 ? kWgSliceRows * 4u : (side == 2 ? kWgSliceRows * 16u : 0u);
+}
+// d_sigma holds n_rows floats: the slice that straddles the end is read element-wise instead (dpre is padded to whole tiles)
+__host__ __device__ inline bool side_vec_in_range(int side, int64_t row0, int64_t n_rows) {
+  return side == 2 || row0 + kWgSliceRows <= n_rows;
+}
 
 // two adjacent bf16 columns (2*cp, 2*cp+1) of row r of a 64-column SWIZZLE_128B slice
 __device__ __forceinline__ float2 ld_img2(const uint8_t* slice, int r, int cp) {
@@ -128,8 +140,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
     const int ai = (sw & 1) | ((sw >> 2) << 1);         // 0..3 over the active warps
     const int k4 = ai, k2 = ai & 1;
     const int a_chunks = pj.a_chunks;
-    const bool do_bias = active && pj.db != nullptr && !(a.dbg_flags & 1);
-    const int side = (!active || (a.dbg_flags & 1)) ? 0 : pj.side;
+    const bool do_bias = active && pj.db != nullptr && !(a.dbg_flags & (1 | 16384));
+    const int side = (!active || (a.dbg_flags & (1 | 8192))) ? 0 : pj.side;
     // reduce over the four row groups that live in one warp (lane bits 3, 4), then one atomic per column and warp
     auto warp_rows_sum = [&](float v) {
       v += __shfl_xor_sync(0xffffffffu, v, 8);
@@ -251,16 +263,25 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
         dst_off = (kWgASlots + bi) * kWgSlice;
       }
       const uint32_t bytes = (uint32_t)n_copies * kWgSlice;
+      // head jobs: the stage's 32 rows of d_sigma (128 B) / dpre (512 B) land with it in the free X slot 4, so the side
+      // warps never wait for a global load (one DRAM latency per stage made the two head jobs latency-bound: 0.15 ms)
+      const uint32_t vec_bytes = side_vec_bytes(job.side);
       for (int s = 0; s < n_stage; ++s, ++it) {
         const uint32_t stage = it % kWgStages, ph = (it / kWgStages) & 1;
+        const int64_t row0 = (int64_t)(t0 + (s >> 2)) * kTileM + (s & 3) * kWgSliceRows;
+        const bool vec = vec_bytes != 0 && side_vec_in_range(job.side, row0, a.n_rows);
         if (lane == 0) {
           mbar_wait(bar_empty + stage, ph ^ 1);
-          mbar_arrive_expect_tx(bar_full + stage, bytes);
+          mbar_arrive_expect_tx(bar_full + stage, bytes + (vec ? vec_bytes : 0u));
         }
         __syncwarp();
         if (lane < n_copies)
           bulk_g2s(smem + stage * kWgStageBytes + dst_off, src + (size_t)(s >> 2) * tile_stride + (s & 3) * kWgSlice,
                    kWgSlice, bar_full + stage);
+        else if (lane == n_copies && vec)
+          bulk_g2s(smem + stage * kWgStageBytes + kWgSideVecOff,
+                   job.side == 1 ? reinterpret_cast<const uint8_t*>(a.d_sigma + row0) : reinterpret_cast<const uint8_t*>(a.dpre + row0 * 4),
+                   vec_bytes, bar_full + stage);
       }
     } else if (warp == 1) {
       // ---------------- UMMA issuer ----------------
@@ -322,8 +343,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       const int t = threadIdx.x - 64;
       const int cb = t & 7, rql = (t >> 3) & 3, sw = t >> 5;
       const int ai = (sw & 1) | ((sw >> 2) << 1);       // 0..3 over the active warps
-      const bool do_bias = job.db != nullptr && !(a.dbg_flags & 1);
-      const int side = (a.dbg_flags & 1) ? 0 : job.side;
+      const bool do_bias = job.db != nullptr && !(a.dbg_flags & (1 | 16384));   // 16384: experiment, heads only
+      const int side = (a.dbg_flags & (1 | 8192)) ? 0 : job.side;               // 8192: experiment, bias sums only
       // bias / sigma head: slice k4 = ai, rows rql*4 .. +3 and the same +16;  rgb head: slice k2 = ai & 1, rows
       // ((ai >> 1) * 8 + rql * 2) .. +1 and the same +16
       const int k4 = ai;
@@ -354,16 +375,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
         float4 dp[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) dp[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (side == 1) {
+        const bool vec = side_vec_in_range(side, row0, a.n_rows);   // the producer applies the same test
+        if (side == 1 && !vec) {           // the slice that straddles the end of d_sigma: element-wise, guarded
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int64_t r = row0 + rql * 4 + (i & 3) + (i >> 2) * 16;
             ds[i] = (r < a.n_rows) ? __ldg(a.d_sigma + r) : 0.f;
           }
-        } else if (side == 2) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            dp[i] = __ldg(reinterpret_cast<const float4*>(a.dpre) + row0 + (ai >> 1) * 8 + rql * 2 + (i & 1) + (i >> 1) * 16);
         }
         mbar_wait(bar_full + stage, ph);
         const uint8_t* st = smem + stage * kWgStageBytes;
@@ -379,11 +397,19 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
             xw[i] = *reinterpret_cast<const uint4*>(st + (kWgASlots + job.side_off + k4) * kWgSlice + off4[i]);
             dep ^= xw[i].w;
           }
+          if (vec) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              ds[i] = *reinterpret_cast<const float*>(st + kWgSideVecOff + (rql * 4 + (i & 3) + (i >> 2) * 16) * 4);
+              dep ^= __float_as_uint(ds[i]);
+            }
+          }
         } else if (side == 2) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             xw[i] = *reinterpret_cast<const uint4*>(st + (kWgASlots + job.side_off + k2) * kWgSlice + off2[i]);
-            dep ^= xw[i].w;
+            dp[i] = *reinterpret_cast<const float4*>(st + kWgSideVecOff + ((ai >> 1) * 8 + rql * 2 + (i & 1) + (i >> 1) * 16) * 16);
+            dep ^= xw[i].w ^ __float_as_uint(dp[i].w);
           }
         }
         // every load above must have RETURNED before the stage goes back to the async-proxy producer: a (never

@@ -16,7 +16,7 @@ z = torch.sort(torch.rand(B, S, device=dev) * 4 + 2, -1)[0]
 params = [p.detach() for p in m.ordered_parameters()]
 packed = m.packed_weights()
 lib = _lib.load()
-for fl in (0, 4):
+for fl in [int(x) for x in os.environ.get('PAIR_FLAGS', '0,4').split(',')]:
   os.environ["NRF_DBG_FLAGS"] = str(fl)
   print("NRF_DBG_FLAGS =", fl)
   for train in (False,):

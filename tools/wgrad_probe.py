@@ -28,19 +28,26 @@ def step():
 
 
 flags = [int(x) for x in sys.argv[1:]] or [0, 1, 2, 3, 8]
+ROUNDS = int(os.environ.get("PROBE_ROUNDS", "1"))      # > 1: round-robin over the flags (clock drift hits all alike)
+acc = {fl: [] for fl in flags}
+for rnd in range(ROUNDS):
+    for fl in flags:
+        os.environ["NRF_DBG_FLAGS"] = str(fl)
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize()
+        lib.nrf_prof_enable(1)
+        for _ in range(5):
+            step()
+        torch.cuda.synchronize()
+        lib.nrf_prof_enable(0)
+        res = {}
+        for kid, name in ((3, "fwd"), (5, "dgrad"), (7, "wgrad")):
+            tot, n, rows = ctypes.c_double(), ctypes.c_int64(), ctypes.c_int64()
+            lib.nrf_prof_read(kid, ctypes.byref(tot), ctypes.byref(n), ctypes.byref(rows))
+            res[name] = tot.value / 5
+        acc[fl].append(res)
 for fl in flags:
-    os.environ["NRF_DBG_FLAGS"] = str(fl)
-    for _ in range(3):
-        step()
-    torch.cuda.synchronize()
-    lib.nrf_prof_enable(1)
-    for _ in range(5):
-        step()
-    torch.cuda.synchronize()
-    lib.nrf_prof_enable(0)
-    res = {}
-    for kid, name in ((3, "fwd"), (5, "dgrad"), (7, "wgrad")):
-        tot, n, rows = ctypes.c_double(), ctypes.c_int64(), ctypes.c_int64()
-        lib.nrf_prof_read(kid, ctypes.byref(tot), ctypes.byref(n), ctypes.byref(rows))
-        res[name] = tot.value / 5
-    print(f"flags={fl}: per step ms " + " ".join(f"{k}={v:.3f}" for k, v in res.items()), flush=True)
+    med = {k: sorted(r[k] for r in acc[fl])[len(acc[fl]) // 2] for k in ("fwd", "dgrad", "wgrad")}
+    ratio = sorted(r["wgrad"] / r["fwd"] for r in acc[fl])[len(acc[fl]) // 2]
+    print(f"flags={fl}: per step ms (median of {ROUNDS}) " + " ".join(f"{k}={v:.3f}" for k, v in med.items()) + f"  wgrad/fwd={ratio:.3f}", flush=True)
