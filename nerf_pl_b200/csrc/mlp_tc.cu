@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
     const uint32_t act_s = smem_u32(s_act), enc_s = smem_u32(s_enc);
     const uint32_t wsig_s = smem_u32(s_aux + AuxOffsets::w_sigma);
     uint32_t acc_par = 0;
-    long long w_acc = 0, t_begin = clock64();
+    long long w_acc = 0, w_free = 0, t_begin = clock64();
     int tn2 = 0;
     // training: every image written to s_act / s_enc is also copied to the stash by the store warp; a buffer may be
     // overwritten once that copy has read it (bar_free).  bit i of `stored`: a copy of buffer i has been requested.
@@ -250,7 +250,10 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
       if (!kTrain) return;
       if ((stored >> buf) & 1u) {
         if (lane == 0) NRF_MARK(warp, 0x4000000 | (mk << 4) | buf);
-        mbar_wait(bar_free + buf, (free_par >> buf) & 1u);
+        const long long tf0 = NRF_HEAVY ? clock64() : 0;
+        if (!(NRF_FWD_DEBUG && (a.dbg_flags & 64)))   // 64: timing experiment, buffers overwritten without waiting for the stash store
+          mbar_wait(bar_free + buf, (free_par >> buf) & 1u);
+        if (NRF_HEAVY) w_free += clock64() - tf0;
         free_par ^= 1u << buf;
       }
       stored |= 1u << buf;
@@ -426,6 +429,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
     if (NRF_FWD_DEBUG == 1 && a.dbg && et == 0) {
       a.dbg[blockIdx.x * 8 + 4] = (unsigned long long)(clock64() - t_begin);
       a.dbg[blockIdx.x * 8 + 5] = (unsigned long long)w_acc;
+      a.dbg[blockIdx.x * 8 + 6] = (unsigned long long)w_free;   // training: waiting for the stash store to have read a buffer
     }
   } else if (kTrain && lane == 0) {
     // ===================== stash store warp (training) =====================

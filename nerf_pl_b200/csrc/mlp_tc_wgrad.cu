@@ -38,6 +38,7 @@ constexpr int kWgThreads = 64 + kWgSideThreads;
 constexpr uint32_t kWgSmBars = kWgStages * kWgStageBytes;
 constexpr uint32_t kWgSmTotal = kWgSmBars + 256;
 constexpr int kWgMaxJobs = 14;
+constexpr int kWgSideArrivals = kWgSideWarps / 2;   // side warps that hold a stage: those of SM sub-partitions 2 and 3 (see below)
 
 struct WgradJob {
   int a_slot, a_chunks;        // G image: first chunk slot in the G stash; 4 (N_out=256), 2 (N_out=128) or 0 (side work only)
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kWgStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1 + kWgSideWarps / 2); }
+    for (int s = 0; s < kWgStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1 + kWgSideArrivals); }
     mbar_init(bar_acc, 1);
     mbar_init(bar_drained, kWgSideWarps);
     for (int s = 0; s < 2; ++s) { mbar_init(bar_uq_full + s, 1); mbar_init(bar_uq_empty + s, 1 + kWgSideWarps); }
@@ -335,7 +336,10 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       if (new_job && prev_job >= 0) flush_group(a.jobs[prev_job]);
       // The arithmetic of the side work competes for issue slots with whatever shares its SM sub-partition; the
       // producer and the UMMA issuer (warps 0, 1) are latency critical, so only the side warps of sub-partitions 2
-      // and 3 (warp & 2) do it (measured: -0.1 ms per step); the others only help with the accumulator flush.
+      // and 3 (warp & 2) do it (measured: -0.1 ms per step); the others only help with the accumulator flush.  (r02:
+      // letting the warps of sub-partitions 0 and 1 merely wait for and release every stage costs +0.1 ms; the four
+      // that do take part cost nothing beyond their arithmetic: with the side warps out of the ring altogether the
+      // kernel runs exactly as fast as with their work skipped, tools/wgrad_probe.py.)
       const bool active = (warp & 2) != 0;
       if (!active) {
         it += n_stage;

@@ -29,4 +29,4 @@ for train in (False, True):
     c = cnt.view(148, 8).double().mean(0).tolist()
     tiles = B * S / 128 / 148
     print(f"train={train} ms={e0.elapsed_time(e1):.3f} per-tile cycles: mma_total={c[0]/tiles:.0f} wait_A={c[1]/tiles:.0f} "
-          f"wait_W={c[2]/tiles:.0f} | epi_total={c[4]/tiles:.0f} epi_wait_acc={c[5]/tiles:.0f}", flush=True)
+          f"wait_W={c[2]/tiles:.0f} | epi_total={c[4]/tiles:.0f} epi_wait_acc={c[5]/tiles:.0f} epi_wait_stash_read={c[6]/tiles:.0f}", flush=True)
