@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
     if (lane == 0) {
       uint32_t stage = 0, ph = 0;
       int tn0 = 0;
+      const uint64_t keep = l2_policy_evict_last();   // the weights stay in L2 under the stash write stream
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
         for (int ci = 0; ci < kChunksPerTile; ++ci) {
           NRF_MARK(0, 0x1000000 | (tile << 8) | ci);
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
                                         (size_t)(ci - kFwdChunksSigma - 4) * kChunkBytes128
                                   : (size_t)ci * kChunkBytes256;
           mbar_arrive_expect_tx(bar_full + stage, bytes);
-          bulk_g2s(s_ring + stage * kChunkBytes256, a.packed + kPackedFwdOff + off, bytes, bar_full + stage);
+          bulk_g2s(s_ring + stage * kChunkBytes256, a.packed + kPackedFwdOff + off, bytes, bar_full + stage, keep);
           if (++stage == kStages) { stage = 0; ph ^= 1; }
         }
       }
@@ -439,6 +440,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
     uint32_t s_par = 0;
     int pending = -1;
     int mk = 0;
+    const uint64_t stream_pol = l2_policy_evict_first();   // written once, read next by wgrad from DRAM anyway
     auto store = [&](int bar_idx, int buf, const uint8_t* src, uint8_t* dst, uint32_t bytes = kActChunkBytes) {   // bar_idx >= 8: bar_s[bar_idx - 8]
       NRF_MARK(18, 0x6000000 | (mk << 4) | bar_idx);
       uint64_t* bar = bar_idx < 8 ? bar_a + bar_idx : bar_s + (bar_idx - 8);
@@ -451,7 +453,7 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
       }
       mbar_wait(bar, par);
       s_par ^= 1u << bar_idx;
-      bulk_s2g(dst, src, bytes);
+      if (!(NRF_FWD_DEBUG && (a.dbg_flags & 128))) bulk_s2g(dst, src, bytes, stream_pol);   // 128: timing experiment, no stash writes
       bulk_commit();
       if (pending >= 0) {
         bulk_wait_read1();

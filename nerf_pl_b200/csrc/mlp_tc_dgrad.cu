@@ -110,13 +110,14 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
   if (warp == 0) {
     if (lane == 0) {
       uint32_t stage = 0, ph = 0;
+      const uint64_t keep = l2_policy_evict_last();   // the weights stay in L2 under the G-image write stream
       for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
         for (int ci = 0; ci < kChunks; ++ci) {
           mbar_wait(bar_empty + stage, ph ^ 1);
           mbar_arrive_expect_tx(bar_full + stage, kChunkBytes256);
           bulk_g2s(s_ring + stage * kChunkBytes256,
                    a.packed + kPackedBwdOff + (size_t)(kFirstChunk + ci) * kChunkBytes256, kChunkBytes256,
-                   bar_full + stage);
+                   bar_full + stage, keep);
           if (++stage == kDgStages) { stage = 0; ph ^= 1; }
         }
       }
@@ -214,7 +215,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
           }
         }
         if (sub == 0) *reinterpret_cast<float4*>(a.dpre + ((size_t)tile * kTileM + row) * 4) = make_float4(dp[0], dp[1], dp[2], 0.f);
-        const uint32_t m = __ldg(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + sub);
+        const uint32_t m = __ldcs(mask_tile + 8 * 128 * 8 + (size_t)row * 4 + sub);   // read once: streaming
         acquire(kDgBarPro);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -241,7 +242,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
         }
         signal(kDgBarPro);
       } else {
-        const uint2 mw2 = __ldg(reinterpret_cast<const uint2*>(mask_tile + ((size_t)7 * 128 + row) * 8 + sub * 2));
+        const uint2 mw2 = __ldcs(reinterpret_cast<const uint2*>(mask_tile + ((size_t)7 * 128 + row) * 8 + sub * 2));
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           const uint32_t m = (c < 2) ? mw2.x : mw2.y;
@@ -280,7 +281,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
         const int t = (kFull ? 8 : 6) - i;  // this epilogue produces G_t
         uint2 mw = make_uint2(0xffffffffu, 0xffffffffu);
         if (t < 8)   // issued before the wait so that the load latency hides behind the MMAs
-          mw = __ldg(reinterpret_cast<const uint2*>(mask_tile + ((size_t)t * 128 + row) * 8 + sub * 2));
+          mw = __ldcs(reinterpret_cast<const uint2*>(mask_tile + ((size_t)t * 128 + row) * 8 + sub * 2));
         const uint32_t b = g & 1u;
         mbar_wait(bar_acc + b, (g >> 1) & 1u);
         tc_fence_after();
@@ -320,6 +321,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
     // epilogue may overwrite it (bar_free).
     uint32_t s_par = 0;
     int pending = -1;
+    const uint64_t stream_pol = l2_policy_evict_first();
     auto store = [&](int idx, bool own_bar, const uint8_t* src, uint8_t* dst, uint32_t bytes) {
       const int pb = own_bar ? 8 + idx : idx;
       uint64_t* bar = own_bar ? bar_s + idx : bar_a + idx;
@@ -332,7 +334,7 @@ __global__ void __launch_bounds__(kDgThreads, 1) mlp_dgrad_kernel(const __grid_c
       }
       mbar_wait(bar, par);
       s_par ^= 1u << pb;
-      bulk_s2g(dst, src, bytes);
+      bulk_s2g(dst, src, bytes, stream_pol);
       bulk_commit();
       if (pending >= 0) {
         bulk_wait_read1();

@@ -267,6 +267,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       // head jobs: the stage's 32 rows of d_sigma (128 B) / dpre (512 B) land with it in the free X slot 4, so the side
       // warps never wait for a global load (one DRAM latency per stage made the two head jobs latency-bound: 0.15 ms)
       const uint32_t vec_bytes = side_vec_bytes(job.side);
+      const uint64_t stream_pol = l2_policy_evict_first();   // every image byte is read once
       for (int s = 0; s < n_stage; ++s, ++it) {
         const uint32_t stage = it % kWgStages, ph = (it / kWgStages) & 1;
         const int64_t row0 = (int64_t)(t0 + (s >> 2)) * kTileM + (s & 3) * kWgSliceRows;
@@ -278,7 +279,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
         __syncwarp();
         if (lane < n_copies)
           bulk_g2s(smem + stage * kWgStageBytes + dst_off, src + (size_t)(s >> 2) * tile_stride + (s & 3) * kWgSlice,
-                   kWgSlice, bar_full + stage);
+                   kWgSlice, bar_full + stage, stream_pol);
         else if (lane == n_copies && vec)
           bulk_g2s(smem + stage * kWgStageBytes + kWgSideVecOff,
                    job.side == 1 ? reinterpret_cast<const uint8_t*>(a.d_sigma + row0) : reinterpret_cast<const uint8_t*>(a.dpre + row0 * 4),
