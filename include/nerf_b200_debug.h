@@ -32,6 +32,10 @@ int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint32_t piece,
  * tcgen05.ld 32x32b .x16 (mode bit 0: .x32); mode bit 1: one thread issues back-to-back MMAs meanwhile.
  * out[2 cta] (u64, device) = cycles of the slowest warp, out[2 cta + 1] = MMAs retired meanwhile. */
 int nrf_dbg_tmem_rate(int warps, int reps, int mode, int grid, void* out, nrf_stream_t stream);
+/* MMA rate (M128 N256 K16, `reps` back to back) under shared-memory traffic.  mode bit 0: A operand from tensor memory;
+ * bit 1: a 4 x 32 KB ring of bulk copies from `src` (>= 1 MB, L2 resident) keeps landing; bit 2: 16 warps keep writing a
+ * 64 KB image with 16-byte shared stores.  out: grid x 2 u64 = {cycles of the MMAs, 32 KB copies landed meanwhile}. */
+int nrf_dbg_mma_contend(int reps, int mode, int grid, const void* src, void* out, nrf_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -4,6 +4,7 @@
 // the forward / dgrad kernels).  DESIGN.md §4 quotes the numbers; tools/stream_bench.py drives it.
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "tc_epilogue.cuh"
 
 namespace nrf {
 namespace tc {
@@ -110,6 +111,78 @@ __global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, int n_cols, u
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
 }
 
+
+// ---- MMA rate under shared-memory traffic ---------------------------------------------------------------
+// One thread issues `reps` M128 x N256 x K16 MMAs back to back (mode bit 0: A operand from tensor memory instead of
+// shared memory) while, with mode bit 1, another thread keeps 32 KB bulk copies from an L2-resident buffer landing in
+// a 4 x 32 KB shared-memory ring (the forward kernel's weight stream) and, with mode bit 2, 16 warps write a 64 KB
+// operand image with 16-byte shared stores over and over (the epilogue's stores).  out[cta * 2] = cycles of the MMAs,
+// out[cta * 2 + 1] = 32 KB copies landed meanwhile.
+__global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, int mode, const uint8_t* src, unsigned long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];   // [0,64K) A image / store target, [64K,96K) B chunk, [96K,224K) ring
+  __shared__ uint64_t bar, bar_ring[4];
+  __shared__ uint32_t s_tmem;
+  __shared__ volatile int s_stop;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(bar_ring + i, 1);
+    fence_barrier_init();
+    s_stop = 0;
+  }
+  for (int i = threadIdx.x; i < 3 * 32768 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  fence_async_smem();
+  if (warp == 1) tmem_alloc(&s_tmem, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s_tmem;
+  if (warp == 1 && lane == 0) {
+    const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
+    const uint64_t a_desc = make_desc_sw128(smem_u32(smem), 16, 1024);
+    const uint64_t b_desc = make_desc_sw128(smem_u32(smem + 65536), 16, 1024);
+    const long long t0 = clock64();
+    if (mode & 1) {
+      for (int r = 0; r < reps; ++r) umma_ts(tmem_base, tmem_base + 256 + 8 * (r & 15), b_desc + 2 * (r & 3), idesc, r >= 1);
+    } else {
+      for (int r = 0; r < reps; ++r) umma_ss(tmem_base, a_desc + 2 * (r & 3) + (uint64_t)((r >> 2) & 3) * (16384 >> 4), b_desc + 2 * (r & 3), idesc, r >= 1);
+    }
+    umma_commit(&bar);
+    mbar_wait(&bar, 0);
+    out[blockIdx.x * 2] = (unsigned long long)(clock64() - t0);
+    s_stop = 1;
+  } else if (warp == 0 && lane == 0 && (mode & 2)) {
+    unsigned long long landed = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < 4; ++i) {
+      mbar_arrive_expect_tx(bar_ring + i, 32768);
+      bulk_g2s(smem + 98304 + i * 32768, src + (size_t)i * 32768, 32768, bar_ring + i);
+    }
+    while (!s_stop) {
+      for (int i = 0; i < 4; ++i) {
+        mbar_wait(bar_ring + i, ph);
+        ++landed;
+        mbar_arrive_expect_tx(bar_ring + i, 32768);
+        bulk_g2s(smem + 98304 + i * 32768, src + (size_t)((landed + i) & 31) * 32768, 32768, bar_ring + i);
+      }
+      ph ^= 1;
+    }
+    for (int i = 0; i < 4; ++i) mbar_wait(bar_ring + i, ph);
+    out[blockIdx.x * 2 + 1] = landed;
+  } else if (warp >= 2 && (mode & 4)) {
+    const int t = threadIdx.x - 64;
+    const uint32_t base = smem_u32(smem);
+    uint32_t k = 0;
+    while (!s_stop) {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) st_shared_v4(base + ((uint32_t)(c * 512 + t) * 16u), k, k, k, k);   // 64 KB per pass
+      ++k;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, 512); }
+}
 
 // ---- TMEM read rate ------------------------------------------------------------------------------------
 // `warps` (4, 8 or 16) warps each read their TMEM lane quarter with tcgen05.ld.32x32b.x16 (or .x32), `reps` passes over
@@ -241,6 +314,17 @@ extern "C" int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint
   NRF_CUDA(cudaFuncSetAttribute(store_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
   store_rate_kernel<<<grid, 32, 65536, as_stream(stream)>>>(static_cast<uint8_t*>(dst), cta_stride, piece, steps, depth,
                                                            static_cast<unsigned long long*>(out));
+  NRF_LAUNCH_CHECK();
+  return NRF_OK;
+}
+
+// MMA rate under shared-memory traffic: see mma_contend_kernel.  src: >= 1 MB device buffer; out: grid x 2 u64.
+extern "C" int nrf_dbg_mma_contend(int reps, int mode, int grid, const void* src, void* out, nrf_stream_t stream) {
+  NRF_REQUIRE(src && out && reps >= 2 && grid >= 1, "nrf_dbg_mma_contend: bad args");
+  const size_t smem_bytes = 98304 + 4 * 32768;
+  NRF_CUDA(cudaFuncSetAttribute(mma_contend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+  mma_contend_kernel<<<grid, 64 + 16 * 32, smem_bytes, as_stream(stream)>>>(reps, mode, static_cast<const uint8_t*>(src),
+                                                                            static_cast<unsigned long long*>(out));
   NRF_LAUNCH_CHECK();
   return NRF_OK;
 }

@@ -453,7 +453,9 @@ __global__ void __launch_bounds__(kTrain ? kThreadsTrain : kThreadsInfer, 1) mlp
       }
       mbar_wait(bar, par);
       s_par ^= 1u << bar_idx;
-      if (!(NRF_FWD_DEBUG && (a.dbg_flags & 128))) bulk_s2g(dst, src, bytes, stream_pol);   // 128: timing experiment, no stash writes
+      // timing experiments: 128 = no stash writes; 256 = every write lands in one L2-resident 64 KB window per CTA
+      if (NRF_FWD_DEBUG && (a.dbg_flags & 256)) dst = a.stash + (size_t)blockIdx.x * 65536 + ((dst - a.stash) & 0xffff);
+      if (!(NRF_FWD_DEBUG && (a.dbg_flags & 128))) bulk_s2g(dst, src, bytes, stream_pol);
       bulk_commit();
       if (pending >= 0) {
         bulk_wait_read1();

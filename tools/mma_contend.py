@@ -1,0 +1,23 @@
+#!/usr/bin/env python
+"""tcgen05.mma rate (M128 N256 K16) with the A operand from shared or tensor memory, alone and while the weight stream
+(bulk copies landing) and the epilogue's shared stores run in the same SM (debug build: nrf_dbg_mma_contend)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from nerf_pl_b200 import _lib
+
+dev = torch.device("cuda:0")
+src = torch.zeros(1 << 20, dtype=torch.uint8, device=dev)
+out = torch.zeros(148 * 2, dtype=torch.int64, device=dev)
+reps = 4096
+names = {0: "A smem", 1: "A tmem", 2: "A smem + landing", 3: "A tmem + landing", 4: "A smem + stores", 5: "A tmem + stores",
+         6: "A smem + landing + stores", 7: "A tmem + landing + stores"}
+for mode in range(8):
+    for _ in range(2):
+        out.zero_()
+        _lib.call("nrf_dbg_mma_contend", reps, mode, 148, src.data_ptr(), out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+    o = out.view(148, 2).double()
+    cyc = o[:, 0].mean().item() / reps
+    land = (o[:, 1] * 32768 / o[:, 0]).mean().item()
+    print(f"mode {mode} ({names[mode]:28s}): {cyc:7.1f} cycles per MMA, landing {land:6.1f} B/clk/SM", flush=True)
