@@ -16,6 +16,7 @@ extern "C" {
 /* Per-CTA cycle counters of the tensor-core forward kernel (8 x uint64 per CTA: [0] MMA-thread total, [1] waiting
  * for A operands, [2] waiting for weights, [4] epilogue total, [5] epilogue waiting for accumulators); NULL = off. */
 void nrf_dbg_set_counters(void* dev_ptr);
+int nrf_dbg_stream_replicas(int replicas);   /* > 0: the next nrf_dbg_stream launches read replica cta % replicas at base + replica * cta_stride */
 int nrf_dbg_stream(const void* base, unsigned long long cta_stride, unsigned long long stream_stride,
                    unsigned long long tile_stride, uint32_t piece, int n_streams, int ppc, int wrap_tiles,
                    int steps, int stages, int grid, nrf_stream_t stream);

@@ -100,6 +100,7 @@ DEBUG_SIGNATURES = {
     "nrf_dbg_tmem_rate": (I, [I, I, I, I, P, P]),
     "nrf_dbg_mma_contend": (I, [I, I, I, P, P, P]),
     "nrf_dbg_store_rate": (I, [P, ctypes.c_uint64, c_uint32, I, I, I, P, P]),
+    "nrf_dbg_stream_replicas": (I, [I]),
     "nrf_dbg_stream": (I, [P, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, c_uint32, I, I, I, I, I, I, P]),
 }
 

@@ -17,6 +17,7 @@ struct StreamArgs {
   int ppc;             // pieces per chunk: consecutive steps walk `ppc` adjacent pieces, then jump by tile_stride
   int wrap_tiles;      // tiles wrap around after this many (0 = never): L2-resident working sets
   int steps, stages;
+  int replicas;        // > 0: CTA b reads replica (b % replicas) at base + replica * cta_stride (L2-resident copies of one blob)
 };
 
 __global__ void __launch_bounds__(64, 1) stream_kernel(const __grid_constant__ StreamArgs a) {
@@ -32,7 +33,7 @@ __global__ void __launch_bounds__(64, 1) stream_kernel(const __grid_constant__ S
   }
   __syncthreads();
   if (warp == 0) {
-    const uint8_t* src = a.base + (size_t)blockIdx.x * a.cta_stride + (size_t)lane * a.stream_stride;
+    const uint8_t* src = a.base + (size_t)(a.replicas > 0 ? blockIdx.x % a.replicas : blockIdx.x) * a.cta_stride + (size_t)lane * a.stream_stride;
     int stage = 0, ph = 0, tile = 0, sub = 0;
     for (int s = 0; s < a.steps; ++s) {
       if (lane == 0) {
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, 
   tc_fence_after();
   const uint32_t tmem_base = s_tmem;
   if (warp == 1 && lane == 0) {
-    const uint32_t idesc = make_idesc_bf16(128, 256, 0, 0);
+    const uint32_t idesc = make_idesc_bf16(128, (mode & 8) ? 128 : ((mode & 16) ? 64 : 256), 0, 0);   // mode bit 3: N = 128, bit 4: N = 64
     const uint64_t a_desc = make_desc_sw128(smem_u32(smem), 16, 1024);
     const uint64_t b_desc = make_desc_sw128(smem_u32(smem + 65536), 16, 1024);
     const long long t0 = clock64();
@@ -169,6 +170,30 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, 
     }
     for (int i = 0; i < 4; ++i) mbar_wait(bar_ring + i, ph);
     out[blockIdx.x * 2 + 1] = landed;
+  } else if (warp >= 2 && (mode & 64)) {
+    // arithmetic-bound warps on every SM sub-partition (the epilogue's FADD / F2FP / LDS mix): does the issuing thread
+    // still get its issue slots?
+    float x0 = (float)threadIdx.x, x1 = 1.f, x2 = 2.f, x3 = 3.f;
+    while (!s_stop) {
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { x0 = fmaf(x0, 1.0001f, x1); x1 = fmaf(x1, 0.9999f, x2); x2 = fmaf(x2, 1.0002f, x3); x3 = fmaf(x3, 0.9998f, x0); }
+    }
+    if (x0 + x1 + x2 + x3 == 12345.f) out[0] = 1;
+  } else if (warp >= 2 && (mode & 32)) {
+    // the epilogue's tensor-memory traffic: every warp reads 2 x 16 accumulator columns and writes 2 x 8 operand columns
+    const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    const int sub = (warp - 2) >> 2;
+    uint32_t va[16], vb[16], pk[8];
+    while (!s_stop) {
+      tmem_ld16(lane_base + 128 + sub * 16, va);
+      tmem_ld16(lane_base + 192 + sub * 16, vb);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 8; ++i) pk[i] = va[2 * i] ^ vb[2 * i + 1];
+      tmem_st8(lane_base + 384 + sub * 8, pk);
+      tmem_st8(lane_base + 416 + sub * 8, pk);
+      tmem_st_wait();
+    }
   } else if (warp >= 2 && (mode & 4)) {
     const int t = threadIdx.x - 64;
     const uint32_t base = smem_u32(smem);
@@ -279,6 +304,10 @@ using namespace nrf;
 using namespace nrf::tc;
 extern "C" int nrf_dbg_mma_rate_n(int reps, int n_cols, int grid, void* out, nrf_stream_t stream);
 
+static int g_stream_replicas = 0;
+// the next nrf_dbg_stream launches read replica (cta % replicas) at base + replica * cta_stride (0: cta * cta_stride)
+extern "C" int nrf_dbg_stream_replicas(int replicas) { g_stream_replicas = replicas; return NRF_OK; }
+
 // Launches `grid` CTAs; returns NRF_OK.  Total bytes moved = grid * steps * n_streams * piece.
 extern "C" int nrf_dbg_stream(const void* base, unsigned long long cta_stride, unsigned long long stream_stride,
                               unsigned long long tile_stride, uint32_t piece, int n_streams, int ppc, int wrap_tiles,
@@ -288,7 +317,7 @@ extern "C" int nrf_dbg_stream(const void* base, unsigned long long cta_stride, u
   NRF_REQUIRE(smem_bytes <= 227 * 1024, "nrf_dbg_stream: ring too large");
   NRF_CUDA(cudaFuncSetAttribute(stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
   StreamArgs a{static_cast<const uint8_t*>(base), cta_stride, stream_stride, tile_stride, piece, n_streams, ppc,
-               wrap_tiles, steps, stages};
+               wrap_tiles, steps, stages, g_stream_replicas};
   stream_kernel<<<grid, 64, smem_bytes, as_stream(stream)>>>(a);
   NRF_LAUNCH_CHECK();
   return NRF_OK;

@@ -532,6 +532,11 @@ static bool use_pair_kernel() {
   const char* e = getenv("NRF_FWD_IMPL");   // read per call: tools/pair_check.py switches it at run time
   return e && e[0] == 'p';
 }
+// NRF_FWD_IMPL=ts selects the experimental tensor-memory / N-split kernel (debug/mlp_tc_ts.cu, tools/ts_check.py)
+static bool use_ts_kernel() {
+  const char* e = getenv("NRF_FWD_IMPL");
+  return e && e[0] == 't';
+}
 #endif
 
 extern "C" size_t nrf_mlp_tc_stash_bytes(int64_t rows, int sigma_only) {
@@ -570,10 +575,16 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
 #if NRF_FWD_DEBUG
     if (use_pair_kernel()) return launch_fwd_pair(!sigma_only, true, a, st);
 #endif
+#if NRF_FWD_DEBUG
+    if (use_ts_kernel()) return launch_fwd_ts(!sigma_only, true, a, st);
+#endif
     return sigma_only ? launch_fwd<false, true>(a, st) : launch_fwd<true, true>(a, st);
   }
 #if NRF_FWD_DEBUG
   if (use_pair_kernel()) return launch_fwd_pair(!sigma_only, false, a, st);
+#endif
+#if NRF_FWD_DEBUG
+  if (use_ts_kernel()) return launch_fwd_ts(!sigma_only, false, a, st);
 #endif
   return sigma_only ? launch_fwd<false, false>(a, st) : launch_fwd<true, false>(a, st);
 }

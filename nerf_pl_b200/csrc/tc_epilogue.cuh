@@ -287,6 +287,28 @@ __device__ __forceinline__ void epi_fwd16(const uint32_t (&v)[16], int c0, uint3
   st_shared_v4(chunk_saddr + rs.piece(p0 + 1), pk[4], pk[5], pk[6], pk[7]);
 }
 
+// the same arithmetic, the 16 bf16 results returned as 8 packed words (lower column in the low half) instead of stored
+template <bool kRelu, bool kMask, bool kDot>
+__device__ __forceinline__ void epi_fwd16_pk(const uint32_t (&v)[16], int c0, uint32_t bias_saddr, uint32_t wdot_saddr,
+                                             uint32_t& sign_reg, float& dot, uint32_t (&pk)[8]) {
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    const float4 b = ld_shared_f4(bias_saddr + (c0 + j) * 4);
+    const float x0 = __uint_as_float(v[j]) + b.x, x1 = __uint_as_float(v[j + 1]) + b.y;
+    const float x2 = __uint_as_float(v[j + 2]) + b.z, x3 = __uint_as_float(v[j + 3]) + b.w;
+    if (kMask) {
+      sign_reg = push_sign(sign_reg, x0); sign_reg = push_sign(sign_reg, x1);
+      sign_reg = push_sign(sign_reg, x2); sign_reg = push_sign(sign_reg, x3);
+    }
+    if (kDot) {
+      const float4 w = ld_shared_f4(wdot_saddr + (c0 + j) * 4);
+      dot += fmaxf(x0, 0.f) * w.x + fmaxf(x1, 0.f) * w.y + fmaxf(x2, 0.f) * w.z + fmaxf(x3, 0.f) * w.w;
+    }
+    pk[j >> 1] = kRelu ? cvt_relu_bf16x2(x0, x1) : cvt_bf16x2(x0, x1);
+    pk[(j >> 1) + 1] = kRelu ? cvt_relu_bf16x2(x2, x3) : cvt_bf16x2(x2, x3);
+  }
+}
+
 template <bool kAddSig>
 __device__ __forceinline__ void epi_dgrad16(const uint32_t (&v)[16], int c, int c0, uint32_t pos_word, float dsig,
                                             uint32_t wsig_saddr, const RowSwz& rs, uint32_t chunk_saddr, int p0) {
