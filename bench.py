@@ -218,7 +218,7 @@ def cpu_frame_call_seconds(n_rays):
 
 
 REFERENCE_SAMPLE_RAYS = 1024
-E2E_IDLE_S = 1.0   # idle before the pipelined end-to-end leg (outside its timed region), see run_gpu()     # bounded sample of the 4096-ray batch per CPU step (~0.7 s on 16 cores)
+E2E_IDLE_S = 1.0   # idle before each of the two K-step burst legs (outside their timed regions), see run_gpu()     # bounded sample of the 4096-ray batch per CPU step (~0.7 s on 16 cores)
 
 
 def run_reference(args):
@@ -460,6 +460,7 @@ def run_gpu(args):
     for _ in range(2):
         graphed(rays_host, rgbs_host)
     sync_all()
+    time.sleep(E2E_IDLE_S)          # both burst legs (this one and the pipelined end-to-end one) start from an idle board
     for i in range(K):
         flush.zero_()
         ev[i][0].record()
