@@ -40,6 +40,12 @@ constexpr uint32_t kWgSmTotal = kWgSmBars + 256;
 constexpr int kWgMaxJobs = 14;
 constexpr int kWgSideArrivals = kWgSideWarps / 2;   // side warps that hold a stage: those of SM sub-partitions 2 and 3 (see below)
 
+#ifndef NRF_FWD_DEBUG
+#define NRF_FWD_DEBUG 0
+#endif
+// experiment flags (tools/wgrad_probe.py) exist in debug builds only; the product kernel carries none of the branches
+#define NRF_WG_DBG(bits) (NRF_FWD_DEBUG && (a.dbg_flags & (bits)))
+
 struct WgradJob {
   int a_slot, a_chunks;        // G image: first chunk slot in the G stash; 4 (N_out=256), 2 (N_out=128) or 0 (side work only)
   int b_n, b_mma;              // X chunks loaded / of which take part in the MMA (rest: side work only)
@@ -141,8 +147,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
     const int ai = (sw & 1) | ((sw >> 2) << 1);         // 0..3 over the active warps
     const int k4 = ai, k2 = ai & 1;
     const int a_chunks = pj.a_chunks;
-    const bool do_bias = active && pj.db != nullptr && !(a.dbg_flags & (1 | 16384));
-    const int side = (!active || (a.dbg_flags & (1 | 8192))) ? 0 : pj.side;
+    const bool do_bias = active && pj.db != nullptr && !NRF_WG_DBG(1 | 16384);
+    const int side = (!active || NRF_WG_DBG(1 | 8192)) ? 0 : pj.side;
     // reduce over the four row groups that live in one warp (lane bits 3, 4), then one atomic per column and warp
     auto warp_rows_sum = [&](float v) {
       v += __shfl_xor_sync(0xffffffffu, v, 8);
@@ -184,7 +190,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
     mbar_wait(bar_acc, grp & 1);
     tc_fence_after();
     const int q = warp & 3, wg = (warp - 2) >> 2;
-    const int halves = (a.dbg_flags & 64) ? 0 : a_chunks >> 1;
+    const int halves = NRF_WG_DBG(64) ? 0 : a_chunks >> 1;
     const int nblk = pj.b_mma * 2;  // 32-column blocks
     const bool vec_ok = (pj.ld & 3) == 0 && (reinterpret_cast<uintptr_t>(pj.dW) & 15) == 0;
     for (int hh = 0; hh < halves; ++hh) {
@@ -296,7 +302,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
           }
           fresh = true;
         }
-        const int halves = (a.dbg_flags & 2) ? 0 : a_chunks >> 1;
+        const int halves = NRF_WG_DBG(2) ? 0 : a_chunks >> 1;
         const int n_main = job.b_mma > 4 ? 4 : job.b_mma;
         const uint32_t idesc_main = make_idesc_bf16(128, 64 * n_main, 1, 1);
         const uint32_t idesc_tail = make_idesc_bf16(128, 64, 1, 1);
@@ -348,8 +354,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
       const int t = threadIdx.x - 64;
       const int cb = t & 7, rql = (t >> 3) & 3, sw = t >> 5;
       const int ai = (sw & 1) | ((sw >> 2) << 1);       // 0..3 over the active warps
-      const bool do_bias = job.db != nullptr && !(a.dbg_flags & (1 | 16384));   // 16384: experiment, heads only
-      const int side = (a.dbg_flags & (1 | 8192)) ? 0 : job.side;               // 8192: experiment, bias sums only
+      const bool do_bias = job.db != nullptr && !NRF_WG_DBG(1 | 16384);   // 16384: experiment, heads only
+      const int side = NRF_WG_DBG(1 | 8192) ? 0 : job.side;               // 8192: experiment, bias sums only
       // bias / sigma head: slice k4 = ai, rows rql*4 .. +3 and the same +16;  rgb head: slice k2 = ai & 1, rows
       // ((ai >> 1) * 8 + rql * 2) .. +1 and the same +16
       const int k4 = ai;
@@ -422,7 +428,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const __grid_c
         if (dep == 0x5bd1e995u) s_unit[2] = (int)dep;   // s_unit[2]: scratch word nobody reads
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_empty + stage);
-        if (a.dbg_flags & 4) continue;   // experiment: loads only, no arithmetic
+        if (NRF_WG_DBG(4)) continue;   // experiment: loads only, no arithmetic
         float f[8];
         if (bias_on) {
 #pragma unroll
@@ -541,7 +547,7 @@ static int launch_wgrad(bool full, const nrf_mlp_grads* g, const uint8_t* xstash
   // granule = 16 tiles (measured best of 2..64 at 4096 x 64/128 rows), less when a CTA's share of a job is small
   const long per_cta = (long)num_tiles * a.n_jobs / sms;
   int tpg = (int)std::max<long>(1, std::min<long>(16, per_cta / 8));
-  if (a.dbg_flags & 8) tpg = 4; else if (a.dbg_flags & 16) tpg = 8; else if (a.dbg_flags & 32) tpg = 32;
+  if (NRF_WG_DBG(8)) tpg = 4; else if (NRF_WG_DBG(16)) tpg = 8; else if (NRF_WG_DBG(32)) tpg = 32;
   long total_gran = 0;
   for (int i = 0; i < a.n_jobs; ++i) {
     WgradJob& j = a.jobs[i];
