@@ -170,7 +170,20 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, 
     }
     for (int i = 0; i < 4; ++i) mbar_wait(bar_ring + i, ph);
     out[blockIdx.x * 2 + 1] = landed;
-  } else if (warp >= 2 && (mode & 64)) {
+  } else if (warp == 2 && lane == 0 && (mode & 128)) {
+    // the stash store: 32 KB bulk stores that READ the A image (the tile the MMAs' A operand comes from in SS mode), two
+    // in flight, into a 64 KB window of `src` per CTA (L2 resident)
+    uint8_t* dst = const_cast<uint8_t*>(src) + (1 << 20) + (size_t)blockIdx.x * 65536;
+    unsigned long long n = 0;
+    while (!s_stop) {
+      bulk_s2g(dst + (n & 1) * 32768, smem + (n & 1) * 32768, 32768);
+      bulk_commit();
+      bulk_wait_read1();
+      ++n;
+    }
+    bulk_wait_all0();
+    out[blockIdx.x * 2 + 1] = n;
+  } else if (warp >= 3 && (mode & 64)) {
     // arithmetic-bound warps on every SM sub-partition (the epilogue's FADD / F2FP / LDS mix): does the issuing thread
     // still get its issue slots?
     float x0 = (float)threadIdx.x, x1 = 1.f, x2 = 2.f, x3 = 3.f;
