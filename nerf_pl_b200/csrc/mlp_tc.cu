@@ -537,6 +537,11 @@ static bool use_ts_kernel() {
   const char* e = getenv("NRF_FWD_IMPL");
   return e && e[0] == 't';
 }
+// NRF_FWD_IMPL=m selects debug/mlp_tc_tmem.cu (hidden activations as tensor-memory operands, N = 256) for every mode
+static int force_impl() {
+  const char* e = getenv("NRF_FWD_IMPL");
+  return (e && e[0] == 'm') ? 2 : 0;
+}
 #endif
 
 extern "C" size_t nrf_mlp_tc_stash_bytes(int64_t rows, int sigma_only) {
@@ -578,6 +583,9 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
 #if NRF_FWD_DEBUG
     if (use_ts_kernel()) return launch_fwd_ts(!sigma_only, true, a, st);
 #endif
+#if NRF_FWD_DEBUG
+    if (force_impl() == 2) return launch_fwd_tmem(!sigma_only, true, a, st);
+#endif
     return sigma_only ? launch_fwd<false, true>(a, st) : launch_fwd<true, true>(a, st);
   }
 #if NRF_FWD_DEBUG
@@ -585,6 +593,9 @@ extern "C" int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float
 #endif
 #if NRF_FWD_DEBUG
   if (use_ts_kernel()) return launch_fwd_ts(!sigma_only, false, a, st);
+#endif
+#if NRF_FWD_DEBUG
+  if (force_impl() == 2) return launch_fwd_tmem(!sigma_only, false, a, st);
 #endif
   return sigma_only ? launch_fwd<false, false>(a, st) : launch_fwd<true, false>(a, st);
 }

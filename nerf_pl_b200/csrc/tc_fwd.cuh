@@ -53,7 +53,9 @@ constexpr int kWarpBase = kMarkBase + 148 * 32;
     if (NRF_FWD_DEBUG && a.dbg && (on)) a.dbg[kWarpBase + (ew) * 64 + (layer) * 4 + (e)] = clock64(); \
   } while (0)
 
-// forward with the activations in tensor memory and N-split layers (mlp_tc_ts.cu)
+// forward with the hidden activations as tensor-memory operands, N = 256 (mlp_tc_tmem.cu): the training forward
+int launch_fwd_tmem(bool full, bool train, const FwdArgs& a, cudaStream_t st);
+// forward with the activations in tensor memory and N-split layers (debug/mlp_tc_ts.cu)
 int launch_fwd_ts(bool full, bool train, const FwdArgs& a, cudaStream_t st);
 // CTA-pair forward (mlp_tc_pair.cu)
 int launch_fwd_pair(bool full, bool train, const FwdArgs& a, cudaStream_t st);

@@ -8,6 +8,7 @@ from nerf_pl_b200 import _lib
 from nerf_pl_b200.mlp import forward_rays
 from nerf_pl_b200.models.nerf import NeRF
 
+IMPL = os.environ.get("TS_IMPL", "ts")   # "ts": debug/mlp_tc_ts.cu, "m": mlp_tc_tmem.cu
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 300
 S = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 dev = torch.device("cuda:0")
@@ -22,12 +23,12 @@ ok = True
 for sigma_only in (False, True):
     for train in (False, True):
         res = {}
-        for impl in ("1cta", "ts"):
+        for impl in ("1cta", IMPL):
             os.environ["NRF_FWD_IMPL"] = impl
             sigma, rgb, saved = forward_rays(m.spec, params, rays, z, sigma_only, train, "bf16", packed=packed)
             torch.cuda.synchronize()
             res[impl] = (sigma.clone(), None if rgb is None else rgb.clone(), None if not train else saved[2].clone())
-        a, b = res["1cta"], res["ts"]
+        a, b = res["1cta"], res[IMPL]
         d_sig = (a[0] - b[0]).abs().max().item()
         d_rgb = 0.0 if a[1] is None else (a[1] - b[1]).abs().max().item()
         d_st = -1 if a[2] is None else int((a[2] != b[2]).sum().item())
@@ -40,7 +41,7 @@ Bb, Sb = 4096, 128
 raysb = torch.cat([torch.zeros(Bb, 3), torch.nn.functional.normalize(torch.randn(Bb, 3), dim=-1), torch.full((Bb, 1), 2.0),
                    torch.full((Bb, 1), 6.0)], -1).to(dev)
 zb = torch.sort(torch.rand(Bb, Sb, device=dev) * 4 + 2, -1)[0]
-for impl in ("1cta", "ts"):
+for impl in ("1cta", IMPL):
     os.environ["NRF_FWD_IMPL"] = impl
     for train in (False, True):
         for _ in range(3):
