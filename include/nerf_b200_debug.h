@@ -35,7 +35,9 @@ int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint32_t piece,
 int nrf_dbg_tmem_rate(int warps, int reps, int mode, int grid, void* out, nrf_stream_t stream);
 /* MMA rate (M128 N256 K16, `reps` back to back) under shared-memory traffic.  mode bit 0: A operand from tensor memory;
  * bit 1: a 4 x 32 KB ring of bulk copies from `src` (>= 1 MB, L2 resident) keeps landing; bit 2: 16 warps keep writing a
- * 64 KB image with 16-byte shared stores.  out: grid x 2 u64 = {cycles of the MMAs, 32 KB copies landed meanwhile}. */
+ * 64 KB image with 16-byte shared stores; bit 7: one thread keeps 32 KB bulk stores READING the A tile in flight; bits 3 / 4:
+ * N = 128 / 64; bit 5: 16 warps of tcgen05.ld / st; bit 6: 16 arithmetic-bound warps.  src >= 1 MB + grid x 64 KB.
+ * out: grid x 3 u64 = {cycles of the MMAs, 32 KB copies landed, 32 KB stores issued meanwhile}. */
 int nrf_dbg_mma_contend(int reps, int mode, int grid, const void* src, void* out, nrf_stream_t stream);
 
 #ifdef __cplusplus

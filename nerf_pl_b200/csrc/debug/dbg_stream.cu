@@ -117,8 +117,8 @@ __global__ void __launch_bounds__(64, 1) mma_rate_kernel(int reps, int n_cols, u
 // One thread issues `reps` M128 x N256 x K16 MMAs back to back (mode bit 0: A operand from tensor memory instead of
 // shared memory) while, with mode bit 1, another thread keeps 32 KB bulk copies from an L2-resident buffer landing in
 // a 4 x 32 KB shared-memory ring (the forward kernel's weight stream) and, with mode bit 2, 16 warps write a 64 KB
-// operand image with 16-byte shared stores over and over (the epilogue's stores).  out[cta * 2] = cycles of the MMAs,
-// out[cta * 2 + 1] = 32 KB copies landed meanwhile.
+// operand image with 16-byte shared stores over and over (the epilogue's stores).  out[cta * 3] = cycles of the MMAs,
+// out[cta * 3 + 1] = 32 KB copies landed meanwhile, out[cta * 3 + 2] = 32 KB bulk stores issued meanwhile (mode bit 7).
 __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, int mode, const uint8_t* src, unsigned long long* out) {
   extern __shared__ __align__(1024) uint8_t smem[];   // [0,64K) A image / store target, [64K,96K) B chunk, [96K,224K) ring
   __shared__ uint64_t bar, bar_ring[4];
@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     mbar_init(&bar, 1);
-    for (int i = 0; i < 4; ++i) mbar_init(bar_ring + i, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(bar_ring + i, (mode & 256) ? 32 : 1);
     fence_barrier_init();
     s_stop = 0;
   }
@@ -150,8 +150,31 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, 
     }
     umma_commit(&bar);
     mbar_wait(&bar, 0);
-    out[blockIdx.x * 2] = (unsigned long long)(clock64() - t0);
+    out[blockIdx.x * 3] = (unsigned long long)(clock64() - t0);
     s_stop = 1;
+  } else if (warp == 0 && (mode & 256)) {
+    // the weight stream through cp.async (LDGSTS) instead of the TMA engine: every lane copies 64 x 16 bytes of a stage
+    unsigned long long landed = 0;
+    uint32_t ph = 0;
+    const uint32_t ring_s = smem_u32(smem + 98304);
+    auto issue = [&](int i, unsigned long long blk) {
+      const uint8_t* g = src + (size_t)(blk & 31) * 32768 + lane * 16;
+      const uint32_t d = ring_s + i * 32768 + lane * 16;
+#pragma unroll 8
+      for (int k = 0; k < 64; ++k) cp_async16(d + k * 512, g + k * 512);
+      cp_async_mbar_arrive(bar_ring + i);
+    };
+    for (int i = 0; i < 4; ++i) issue(i, i);
+    while (!s_stop) {
+      for (int i = 0; i < 4; ++i) {
+        mbar_wait(bar_ring + i, ph);
+        ++landed;
+        issue(i, landed + i);
+      }
+      ph ^= 1;
+    }
+    for (int i = 0; i < 4; ++i) mbar_wait(bar_ring + i, ph);
+    if (lane == 0) out[blockIdx.x * 3 + 1] = landed;
   } else if (warp == 0 && lane == 0 && (mode & 2)) {
     unsigned long long landed = 0;
     uint32_t ph = 0;
@@ -169,7 +192,7 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, 
       ph ^= 1;
     }
     for (int i = 0; i < 4; ++i) mbar_wait(bar_ring + i, ph);
-    out[blockIdx.x * 2 + 1] = landed;
+    out[blockIdx.x * 3 + 1] = landed;
   } else if (warp == 2 && lane == 0 && (mode & 128)) {
     // the stash store: 32 KB bulk stores that READ the A image (the tile the MMAs' A operand comes from in SS mode), two
     // in flight, into a 64 KB window of `src` per CTA (L2 resident)
@@ -182,7 +205,7 @@ __global__ void __launch_bounds__(64 + 16 * 32, 1) mma_contend_kernel(int reps, 
       ++n;
     }
     bulk_wait_all0();
-    out[blockIdx.x * 2 + 1] = n;
+    out[blockIdx.x * 3 + 2] = n;
   } else if (warp >= 3 && (mode & 64)) {
     // arithmetic-bound warps on every SM sub-partition (the epilogue's FADD / F2FP / LDS mix): does the issuing thread
     // still get its issue slots?
@@ -360,7 +383,7 @@ extern "C" int nrf_dbg_store_rate(void* dst, unsigned long long cta_stride, uint
   return NRF_OK;
 }
 
-// MMA rate under shared-memory traffic: see mma_contend_kernel.  src: >= 1 MB device buffer; out: grid x 2 u64.
+// MMA rate under shared-memory traffic: see mma_contend_kernel.  src: >= 1 MB + grid x 64 KB device buffer; out: grid x 3 u64.
 extern "C" int nrf_dbg_mma_contend(int reps, int mode, int grid, const void* src, void* out, nrf_stream_t stream) {
   NRF_REQUIRE(src && out && reps >= 2 && grid >= 1, "nrf_dbg_mma_contend: bad args");
   const size_t smem_bytes = 98304 + 4 * 32768;
