@@ -203,6 +203,7 @@ size_t nrf_mlp_tc_stash_bytes(int64_t rows, int sigma_only);
 int nrf_mlp_tc_fwd(const void* packed, const float* rays, const float* z, int64_t n_rays, int n_samples,
                    int sigma_only, float* sigma_out, float* rgb_out, void* stash, size_t stash_bytes,
                    nrf_stream_t stream);
+/* d_sigma (rows) must be 16-byte aligned: slices of it are bulk-copied into the weight-gradient kernel's stages. */
 size_t nrf_mlp_tc_bwd_workspace_bytes(int64_t rows, int sigma_only);
 int nrf_mlp_tc_bwd(const void* packed, const nrf_mlp_grads* g, const float* rays, const float* z,
                    int64_t n_rays, int n_samples, int sigma_only, const float* d_sigma, const float* d_rgb,

@@ -591,6 +591,7 @@ extern "C" int nrf_mlp_tc_bwd(const void* packed, const nrf_mlp_grads* g, const 
   if (n_rays == 0) return NRF_OK;
   NRF_REQUIRE(packed && g && d_sigma && stash && workspace, "nrf_mlp_tc_bwd: null pointer");
   NRF_REQUIRE(sigma_only || (d_rgb && rgb_out), "nrf_mlp_tc_bwd: full mode needs d_rgb and rgb_out");
+  NRF_REQUIRE((reinterpret_cast<uintptr_t>(d_sigma) & 15) == 0, "nrf_mlp_tc_bwd: d_sigma must be 16-byte aligned (bulk-copied into the wgrad stages)");
   const bool full = !sigma_only;
   const int64_t rows = n_rays * n_samples;
   const int tiles = (int)((rows + kTileM - 1) / kTileM);
